@@ -1,0 +1,134 @@
+/* d4est_b200.h -- C ABI of the B200 (sm_100a) matrix-free SIPG/DG Laplacian path.
+ *
+ * Plain C: pointers and sizes only, no torch / C++ types.  This is the drop-in
+ * boundary behind d4est's operator API.  Every entry point names the reference
+ * interface (file:line under the d4est tree) it replaces.  The d4est-facing
+ * glue that calls these from d4est's own structs (p4est_t, d4est_mesh_data_t,
+ * d4est_elliptic_data_t ...) is include/d4est_b200_glue.h; see INTEGRATION.md.
+ *
+ * Conventions:
+ *   - 3-D only.  N = deg+1 GLL nodes per direction, Nq = deg_quad+1 quadrature
+ *     points per direction.  Node id = i_r + N*(i_s + N*i_t) (r fastest).
+ *   - nodal vectors are element-concatenated in p4est local order; element e
+ *     starts at node_off[e] (d4est: ed->nodal_stride, Mesh/d4est_mesh.c:2441).
+ *   - all arithmetic FP64.
+ *   - return value 0 = success; nonzero = D4B_E* error code, message via
+ *     d4b_last_error().  The reference itself has no error returns (it aborts,
+ *     Utilities/d4est_util.h:171); the glue layer turns nonzero into D4EST_ABORT.
+ */
+#ifndef D4EST_B200_H
+#define D4EST_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define D4B_MAX_DEG 11      /* N  <= 12 */
+#define D4B_MAX_DEGQ 15     /* Nq <= 16 */
+
+enum { D4B_OK = 0, D4B_EINVAL = 1, D4B_ECUDA = 2, D4B_ENOMEM = 3, D4B_ENCCL = 4, D4B_ENODEV = 5 };
+
+enum { D4B_QUAD_GAUSS_LEGENDRE = 0, D4B_QUAD_GAUSS_LOBATTO = 1 };
+
+/* ------------------------------------------------------------------------
+ * Half-mortar record: one (local element, face, sub-face) side of an interface
+ * or a physical-boundary face.  The face iterator of the reference
+ * (Mesh/d4est_mortars_with_opt.c:612-806) visits every interface once per side
+ * ("s_m" loop :659); one record is emitted per local "minus" element per
+ * mortar sub-face, so each element owns all records that write into its Au and
+ * no two records of different elements write the same output (no atomics).
+ * ---------------------------------------------------------------------- */
+typedef struct d4b_hm {
+  int32_t nbr;      /* neighbour element: local id, n_local+ghost id, or -1 = boundary   */
+  int8_t f_m;       /* my p4est face 0..5 (Appendix A.2)                                */
+  int8_t f_p;       /* neighbour's face                                                 */
+  int8_t tcode;     /* bit0: axes aligned, bit1: flip fast axis, bit2: flip slow axis:
+                       m-order point (a,b) -> p-order point, restating
+                       d4est_operators_reorient_face_data (dGMath/d4est_operators.c:1993) */
+  int8_t child_m;   /* -1: my whole face is the mortar; 0..3: mortar = this sub-face of
+                       my face (I am the coarse side), bits (fast, slow)                */
+  int8_t child_p;   /* same for the neighbour, child index in the neighbour's own frame */
+  int8_t degq;      /* mortar quadrature degree = max(deg_quad_m, deg_quad_p)
+                       (dGMath/d4est_laplacian_with_opt_flux.c:302-316)                 */
+  int8_t face_slot; /* 0..5 = f_m (kept for alignment / debugging)                      */
+  int8_t pad;
+  int64_t fac_off;  /* offset in doubles into fac[]: [7][Nqm^2] = a_m[3], a_p[3], sj*sigma
+                       (interior) or [4][Nqm^2] = a_m[3], sj*sigma (boundary)            */
+  int64_t g_off;    /* boundary only: offset into bc_g[] of Nqm^2 Dirichlet values, or -1 */
+  int64_t pad2;
+} d4b_hm_t;         /* 40 bytes */
+
+/* Flat, pointer-and-size description of one mesh level on one rank.  Built by the
+ * glue from d4est structs (d4est_mesh_data_t Mesh/d4est_mesh.h:117-162,
+ * d4est_element_data_t Mesh/d4est_element_data.h:13-46) or synthetically
+ * (d4b_brick_desc_*).  All arrays are host pointers owned by the caller and are
+ * copied to HBM by d4b_mesh_create. */
+typedef struct d4b_mesh_desc {
+  int32_t n_local;          /* local elements                                          */
+  int32_t n_ghost;          /* ghost elements (d4est_ghost_t Mesh/d4est_ghost.h:7)     */
+  int32_t quad_type;        /* D4B_QUAD_*  ([quadrature] name = legendre | lobatto)    */
+  int32_t reserved;
+  const int32_t *deg;       /* [n_local+n_ghost]                                       */
+  const int64_t *node_off;  /* [n_local+n_ghost+1]; ghosts continue after local_nodes  */
+  const int32_t *degq;      /* [n_local]  deg_quad                                     */
+  const int64_t *quad_off;  /* [n_local+1] volume quadrature node offsets              */
+  const double *G;          /* [6*quad_off[n_local]] element-blocked symmetric metric:
+                               G[6*quad_off[e] + c*Nq^3 + q], c = (00,01,02,11,12,22),
+                               G_ll' = w J sum_k dr_l/dx_k dr_l'/dx_k
+                               (Quadrature/d4est_quadrature.c:339-375)                  */
+  const int32_t *hm_begin;  /* [n_local+1] CSR of half-mortar records per element      */
+  const d4b_hm_t *hm;       /* [hm_begin[n_local]]                                     */
+  const double *fac;        /* mortar factor pool                                      */
+  int64_t n_fac;
+  const double *bc_g;       /* boundary-value pool (may be NULL when homogeneous)      */
+  int64_t n_bc_g;
+  /* halo (d4est_ghost_data_exchange Mesh/d4est_ghost_data.c:143): ghost elements are
+   * ordered by owner rank as in p4est's ghost layer                                    */
+  int32_t n_peers;
+  int32_t reserved2;
+  const int32_t *peer_rank;   /* [n_peers]                                             */
+  const int32_t *send_begin;  /* [n_peers+1] into send_elem                            */
+  const int32_t *send_elem;   /* local element ids (mirrors), per peer                 */
+  const int32_t *recv_begin;  /* [n_peers+1] ghost element index ranges per peer       */
+} d4b_mesh_desc_t;
+
+typedef struct d4b_mesh d4b_mesh_t; /* opaque: device-resident level */
+
+const char *d4b_last_error(void);
+int d4b_device_count(int *count);
+int d4b_set_device(int dev);
+const char *d4b_version(void);
+
+/* ---- mesh residency (hook: d4est_mesh_update, Mesh/d4est_mesh.c:2790) ------------ */
+int d4b_mesh_create(const d4b_mesh_desc_t *desc, d4b_mesh_t **out);
+void d4b_mesh_destroy(d4b_mesh_t *m);
+int64_t d4b_mesh_local_nodes(const d4b_mesh_t *m);
+int64_t d4b_mesh_ghost_nodes(const d4b_mesh_t *m);
+int64_t d4b_mesh_bytes(const d4b_mesh_t *m);          /* HBM footprint of the level    */
+int64_t d4b_mesh_algorithmic_bytes(const d4b_mesh_t *m); /* SURVEY 8(d) bytes per apply */
+
+/* ---- operator apply: replaces d4est_laplacian_with_opt_apply_aij
+ *      (dGMath/d4est_laplacian_with_opt.c:289) and its twin d4est_laplacian_apply_aij
+ *      (dGMath/d4est_laplacian.c:317).  Au is overwritten.                            */
+int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host);
+int d4b_apply_dev(d4b_mesh_t *m, const double *u_dev, double *Au_dev, void *cuda_stream);
+/* ghost values supplied by the caller (single-process tests of the N>1 layout) */
+int d4b_set_ghost_host(d4b_mesh_t *m, const double *ughost_host);
+int64_t d4b_kernel_launches(void);   /* number of d4b kernels launched so far          */
+
+/* ---- device vectors / BLAS-1 (LinearAlgebra/d4est_linalg.c:179-235) -------------- */
+int d4b_dev_alloc(size_t bytes, void **dptr);
+int d4b_dev_free(void *dptr);
+int d4b_h2d(void *dst_dev, const void *src_host, size_t bytes, void *cuda_stream);
+int d4b_d2h(void *dst_host, const void *src_dev, size_t bytes, void *cuda_stream);
+int d4b_sync(void *cuda_stream);
+int d4b_host_alloc_pinned(size_t bytes, void **hptr);
+int d4b_host_free_pinned(void *hptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
