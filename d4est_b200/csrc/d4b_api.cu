@@ -1,0 +1,231 @@
+/* d4b_api.cu -- C-ABI entry points (include/d4est_b200.h): residency, apply, copies. */
+#include "d4b_internal.h"
+#include "d4b_ops.h"
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <atomic>
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void d4b_set_error(const char *fmt, ...)
+{ va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap); }
+void d4b_count_launch(int n) { g_launches += n; }
+
+int d4b_launch_generic(const d4b_mesh *m, const double *u, double *Au, const int32_t *elem_list,
+                       int n_list, cudaStream_t st);
+size_t d4b_generic_smem_bytes(int NX, int NQX);
+int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st, int *handled);
+
+extern "C" {
+
+const char *d4b_last_error(void) { return g_err; }
+const char *d4b_version(void) { return "d4est_b200 0.1 (sm_100a)"; }
+int64_t d4b_kernel_launches(void) { return (int64_t)g_launches.load(); }
+
+int d4b_device_count(int *count)
+{
+  int n = 0; cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) { n = 0; cudaGetLastError(); }
+  *count = n; return D4B_OK;
+}
+int d4b_set_device(int dev) { D4B_CUDA(cudaSetDevice(dev)); return D4B_OK; }
+
+int d4b_dev_alloc(size_t bytes, void **p) { D4B_CUDA(cudaMalloc(p, bytes ? bytes : 8)); return D4B_OK; }
+int d4b_dev_free(void *p) { D4B_CUDA(cudaFree(p)); return D4B_OK; }
+int d4b_h2d(void *d, const void *s, size_t n, void *st)
+{ D4B_CUDA(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, (cudaStream_t)st)); return D4B_OK; }
+int d4b_d2h(void *d, const void *s, size_t n, void *st)
+{ D4B_CUDA(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, (cudaStream_t)st)); return D4B_OK; }
+int d4b_sync(void *st) { D4B_CUDA(cudaStreamSynchronize((cudaStream_t)st)); return D4B_OK; }
+int d4b_host_alloc_pinned(size_t n, void **p) { D4B_CUDA(cudaMallocHost(p, n ? n : 8)); return D4B_OK; }
+int d4b_host_free_pinned(void *p) { D4B_CUDA(cudaFreeHost(p)); return D4B_OK; }
+
+} /* extern C */
+
+/* ------------------------------------------------------------ 1-D operator pool */
+static d4b_ops_dev g_ops[2];
+static bool g_ops_ready[2] = {false, false};
+
+const d4b_ops_dev *d4b_ops_device(int qt)
+{
+  if (qt < 0 || qt > 1) { d4b_set_error("bad quad_type %d", qt); return nullptr; }
+  if (g_ops_ready[qt]) return &g_ops[qt];
+  std::vector<double> pool;
+  d4b_ops_index &ix = g_ops[qt].idx;
+  double buf[D4B_OPS_MAXN * D4B_OPS_MAXN], x[D4B_OPS_MAXN], w[D4B_OPS_MAXN];
+  for (int dg = 0; dg < D4B_NDEG; dg++) {
+    int N = dg + 1;
+    if (dg == 0) { buf[0] = 0.; } else d4b_ops_diff(dg, buf);
+    ix.D[dg] = (int)pool.size(); pool.insert(pool.end(), buf, buf + N * N);
+    ix.Dt[dg] = (int)pool.size();
+    for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) pool.push_back(buf[j * N + i]);
+  }
+  for (int dq = 0; dq < D4B_NDEGQ; dq++) {
+    if (qt == 1 && dq == 0) { x[0] = 0.; w[0] = 2.; } else d4b_ops_quad(dq, qt, x, w);
+    ix.w[dq] = (int)pool.size(); pool.insert(pool.end(), w, w + dq + 1);
+  }
+  for (int dg = 0; dg < D4B_NDEG; dg++)
+    for (int dq = 0; dq < D4B_NDEGQ; dq++)
+      for (int c = 0; c < 3; c++) {
+        ix.I[dg][dq][c] = (int)pool.size();
+        if (dg == 0 || (qt == 1 && dq == 0)) { pool.insert(pool.end(), (size_t)(dg + 1) * (dq + 1), 1.0); continue; }
+        d4b_ops_interp(dg, dq, qt, c - 1, buf);
+        pool.insert(pool.end(), buf, buf + (dg + 1) * (dq + 1));
+      }
+  double *d = nullptr;
+  if (cudaMalloc(&d, pool.size() * sizeof(double)) != cudaSuccess ||
+      cudaMemcpy(d, pool.data(), pool.size() * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess) {
+    d4b_set_error("ops pool upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  g_ops[qt].pool = d; g_ops_ready[qt] = true;
+  return &g_ops[qt];
+}
+
+template <class T> static int upload(T **dst, const T *src, size_t n, int64_t *bytes)
+{
+  *dst = nullptr;
+  D4B_CUDA(cudaMalloc((void **)dst, (n ? n : 1) * sizeof(T)));
+  if (n) D4B_CUDA(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+  *bytes += (int64_t)(n * sizeof(T));
+  return D4B_OK;
+}
+
+extern "C" {
+
+int d4b_mesh_create(const d4b_mesh_desc_t *D, d4b_mesh_t **out)
+{
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    d4b_set_error("no CUDA device: d4est_b200 has no CPU fallback"); return D4B_ENODEV;
+  }
+  if (!D || D->n_local < 0 || D->n_ghost < 0) { d4b_set_error("bad descriptor"); return D4B_EINVAL; }
+  const int nl = D->n_local, ne = nl + D->n_ghost;
+  d4b_mesh *m = (d4b_mesh *)calloc(1, sizeof(d4b_mesh));
+  m->n_local = nl; m->n_ghost = D->n_ghost; m->quad_type = D->quad_type;
+  m->local_nodes = D->node_off[nl]; m->ghost_nodes = D->node_off[ne] - D->node_off[nl];
+  m->total_quad = D->quad_off[nl]; m->n_hm = D->hm_begin[nl]; m->n_fac = D->n_fac; m->n_bc_g = D->n_bc_g;
+  int64_t alg = 0;
+  for (int e = 0; e < ne; e++) {
+    if (D->deg[e] < 1 || D->deg[e] > D4B_MAX_DEG) { d4b_set_error("deg[%d]=%d out of range", e, D->deg[e]); free(m); return D4B_EINVAL; }
+    if (D->deg[e] > m->max_deg_ext) m->max_deg_ext = D->deg[e];
+    int64_t N = D->deg[e] + 1;
+    if (D->node_off[e + 1] - D->node_off[e] != N * N * N) { d4b_set_error("node_off inconsistent at %d", e); free(m); return D4B_EINVAL; }
+  }
+  for (int e = 0; e < nl; e++) {
+    if (D->degq[e] < 0 || D->degq[e] > D4B_MAX_DEGQ) { d4b_set_error("degq[%d] out of range", e); free(m); return D4B_EINVAL; }
+    if (D->deg[e] > m->max_deg) m->max_deg = D->deg[e];
+    if (D->degq[e] > m->max_degq) m->max_degq = D->degq[e];
+    int64_t N = D->deg[e] + 1, Nq = D->degq[e] + 1;
+    alg += 16 * N * N * N + 48 * Nq * Nq * Nq;
+  }
+  for (int64_t r = 0; r < m->n_hm; r++) {
+    const d4b_hm_t &h = D->hm[r];
+    if (h.degq > D4B_MAX_DEGQ || h.nbr >= ne || h.f_m < 0 || h.f_m > 5) { d4b_set_error("bad half-mortar %lld", (long long)r); free(m); return D4B_EINVAL; }
+    if (h.degq > m->max_degq) m->max_degq = h.degq;
+    int64_t n2 = (int64_t)(h.degq + 1) * (h.degq + 1);
+    alg += (h.nbr >= 0) ? 28 * n2 : 32 * n2; /* 7 doubles per unique mortar point, 4 on the boundary */
+  }
+  m->alg_bytes = alg;
+  m->generic_smem = d4b_generic_smem_bytes(m->max_deg_ext + 1, m->max_degq + 1);
+  if (m->generic_smem > 227 * 1024) {
+    d4b_set_error("degrees too high for the generic kernel: needs %zu B shared memory", m->generic_smem);
+    free(m); return D4B_EINVAL;
+  }
+  int rc;
+#define UP(field, src, n) if ((rc = upload(&m->field, src, (size_t)(n), &m->bytes)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
+  UP(deg, D->deg, ne) UP(node_off, D->node_off, ne + 1) UP(degq, D->degq, nl) UP(quad_off, D->quad_off, nl + 1)
+  UP(G, D->G, 6 * m->total_quad) UP(hm_begin, D->hm_begin, nl + 1) UP(hm, D->hm, m->n_hm)
+  UP(fac, D->fac, m->n_fac) UP(bc_g, D->bc_g, m->n_bc_g)
+#undef UP
+  D4B_CUDA(cudaMalloc((void **)&m->u_ghost, (m->ghost_nodes ? m->ghost_nodes : 1) * sizeof(double)));
+  D4B_CUDA(cudaMemset(m->u_ghost, 0, (m->ghost_nodes ? m->ghost_nodes : 1) * sizeof(double)));
+  D4B_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+  /* halo lists */
+  m->n_peers = D->n_peers;
+  if (D->n_peers > 0) {
+    int np = D->n_peers;
+    m->peer_rank_h = (int32_t *)malloc(np * sizeof(int32_t)); memcpy(m->peer_rank_h, D->peer_rank, np * sizeof(int32_t));
+    m->send_begin_h = (int32_t *)malloc((np + 1) * sizeof(int32_t)); memcpy(m->send_begin_h, D->send_begin, (np + 1) * sizeof(int32_t));
+    m->recv_begin_h = (int32_t *)malloc((np + 1) * sizeof(int32_t)); memcpy(m->recv_begin_h, D->recv_begin, (np + 1) * sizeof(int32_t));
+    m->send_node_begin_h = (int64_t *)calloc(np + 1, sizeof(int64_t));
+    m->recv_node_begin_h = (int64_t *)calloc(np + 1, sizeof(int64_t));
+    int64_t sn = 0;
+    for (int p = 0; p < np; p++) {
+      m->send_node_begin_h[p] = sn;
+      for (int j = D->send_begin[p]; j < D->send_begin[p + 1]; j++) {
+        int e = D->send_elem[j]; sn += D->node_off[e + 1] - D->node_off[e];
+      }
+      m->recv_node_begin_h[p] = D->node_off[nl + D->recv_begin[p]] - D->node_off[nl];
+    }
+    m->send_node_begin_h[np] = sn;
+    m->recv_node_begin_h[np] = D->node_off[nl + D->recv_begin[np]] - D->node_off[nl];
+    m->send_nodes = sn;
+    int64_t dummy = 0;
+    if ((rc = upload(&m->send_elem, D->send_elem, (size_t)D->send_begin[np], &dummy)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
+    D4B_CUDA(cudaMalloc((void **)&m->send_buf, (sn ? sn : 1) * sizeof(double)));
+  }
+  *out = m;
+  return D4B_OK;
+}
+
+void d4b_mesh_destroy(d4b_mesh_t *m)
+{
+  if (!m) return;
+  cudaFree(m->deg); cudaFree(m->node_off); cudaFree(m->degq); cudaFree(m->quad_off); cudaFree(m->G);
+  cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost);
+  cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->send_elem); cudaFree(m->send_buf);
+  free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
+  free(m->send_node_begin_h); free(m->recv_node_begin_h);
+  if (m->stream) cudaStreamDestroy(m->stream);
+  free(m);
+}
+
+int64_t d4b_mesh_local_nodes(const d4b_mesh_t *m) { return m->local_nodes; }
+int64_t d4b_mesh_ghost_nodes(const d4b_mesh_t *m) { return m->ghost_nodes; }
+int64_t d4b_mesh_bytes(const d4b_mesh_t *m) { return m->bytes; }
+int64_t d4b_mesh_algorithmic_bytes(const d4b_mesh_t *m) { return m->alg_bytes; }
+
+int d4b_set_ghost_host(d4b_mesh_t *m, const double *ug)
+{
+  if (m->ghost_nodes) D4B_CUDA(cudaMemcpy(m->u_ghost, ug, m->ghost_nodes * sizeof(double), cudaMemcpyHostToDevice));
+  return D4B_OK;
+}
+
+int d4b_apply_dev(d4b_mesh_t *m, const double *u, double *Au, void *stream)
+{
+  cudaStream_t st = (cudaStream_t)stream;
+  int handled = 0;
+  int rc = d4b_launch_fast(m, u, Au, st, &handled);
+  if (rc != D4B_OK) return rc;
+  if (!handled) rc = d4b_launch_generic(m, u, Au, nullptr, 0, st);
+  return rc;
+}
+
+int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
+{
+  size_t nb = (size_t)m->local_nodes * sizeof(double);
+  if (!m->u_stage) {
+    D4B_CUDA(cudaMalloc((void **)&m->u_stage, nb ? nb : 8));
+    D4B_CUDA(cudaMalloc((void **)&m->Au_stage, nb ? nb : 8));
+  }
+  D4B_CUDA(cudaMemcpyAsync(m->u_stage, u_host, nb, cudaMemcpyHostToDevice, m->stream));
+  int rc = d4b_apply_dev(m, m->u_stage, m->Au_stage, m->stream);
+  if (rc != D4B_OK) return rc;
+  D4B_CUDA(cudaMemcpyAsync(Au_host, m->Au_stage, nb, cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  return D4B_OK;
+}
+
+} /* extern C */
+
+/* fast templated kernels are added in d4b_apply_fast.cu; until an element class has one
+ * the generic kernel handles it */
+__attribute__((weak)) int d4b_launch_fast(const d4b_mesh *, const double *, double *, cudaStream_t, int *handled)
+{ *handled = 0; return D4B_OK; }

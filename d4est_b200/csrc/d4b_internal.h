@@ -1,0 +1,48 @@
+/* d4b_internal.h -- device-side data model shared by the .cu files (not part of the ABI). */
+#ifndef D4B_INTERNAL_H
+#define D4B_INTERNAL_H
+#include "../../include/d4est_b200.h"
+#include <cuda_runtime.h>
+
+#define D4B_NDEG 12   /* deg 0..11  */
+#define D4B_NDEGQ 16  /* degq 0..15 */
+
+/* offsets (in doubles) into the 1-D operator pool of one quadrature type */
+struct d4b_ops_index {
+  int D[D4B_NDEG];                 /* N x N,   D[i*N+j] = l_j'(x_i)                      */
+  int Dt[D4B_NDEG];                /* transpose                                          */
+  int w[D4B_NDEGQ];                /* Nq quadrature weights                              */
+  int I[D4B_NDEG][D4B_NDEGQ][3];   /* Nq x N interpolation GLL->quad; [0] full face,
+                                      [1] child 0 (lower half), [2] child 1 (upper half) */
+};
+
+struct d4b_ops_dev {
+  d4b_ops_index idx;
+  const double *pool;              /* device pointer */
+};
+
+/* device-resident mesh level */
+struct d4b_mesh {
+  int n_local, n_ghost, quad_type, max_deg, max_degq, max_deg_ext;
+  int64_t local_nodes, ghost_nodes, total_quad, n_hm, n_fac, n_bc_g;
+  int32_t *deg; int64_t *node_off; int32_t *degq; int64_t *quad_off;
+  double *G; int32_t *hm_begin; d4b_hm_t *hm; double *fac; double *bc_g;
+  double *u_ghost;                 /* [ghost_nodes] received halo                        */
+  double *u_stage, *Au_stage;      /* staging for d4b_apply_host                         */
+  int64_t bytes, alg_bytes;
+  size_t generic_smem;
+  /* halo lists */
+  int n_peers; int32_t *peer_rank_h, *send_begin_h, *recv_begin_h; int32_t *send_elem;
+  int64_t *send_node_begin_h, *recv_node_begin_h; double *send_buf; int64_t send_nodes;
+  cudaStream_t stream;
+};
+
+void d4b_set_error(const char *fmt, ...);
+const d4b_ops_dev *d4b_ops_device(int quad_type); /* lazily built + uploaded */
+void d4b_count_launch(int n);
+
+#define D4B_CUDA(call)                                                                   \
+  do { cudaError_t e_ = (call);                                                          \
+    if (e_ != cudaSuccess) { d4b_set_error("%s:%d %s: %s", __FILE__, __LINE__, #call,   \
+                                           cudaGetErrorString(e_)); return D4B_ECUDA; } } while (0)
+#endif

@@ -31,7 +31,7 @@ static void legendre(int n, ld x, ld *p, ld *dp)
 void d4b_ops_gauss(int n, double *x, double *w)
 { /* n points, ascending */
   for (int i = 0; i < n; i++) {
-    ld z = -cosl(M_PIl * (i + 0.75L) / (n + 0.5L));
+    ld z = -cosl(3.14159265358979323846264338327950288L * (i + 0.75L) / (n + 0.5L));
     ld p, dp;
     for (int it = 0; it < 100; it++) {
       legendre(n, z, &p, &dp);
@@ -54,7 +54,7 @@ void d4b_ops_gll(int deg, double *x, double *w)
   int n = deg;
   x[0] = -1.0; x[n] = 1.0;
   for (int i = 1; i < n; i++) {
-    ld z = -cosl(M_PIl * i / n);
+    ld z = -cosl(3.14159265358979323846264338327950288L * i / n);
     for (int it = 0; it < 100; it++) {
       /* q = P_n', q' from Legendre ODE: (1-z^2) P'' = 2 z P' - n(n+1) P */
       ld p, dp; legendre(n, z, &p, &dp);

@@ -55,6 +55,7 @@ typedef struct d4b_hm {
                        (dGMath/d4est_laplacian_with_opt_flux.c:302-316)                 */
   int8_t face_slot; /* 0..5 = f_m (kept for alignment / debugging)                      */
   int8_t pad;
+  int32_t pad0;     /* explicit: keeps the 8-byte fields aligned, sizeof == 40        */
   int64_t fac_off;  /* offset in doubles into fac[]: [7][Nqm^2] = a_m[3], a_p[3], sj*sigma
                        (interior) or [4][Nqm^2] = a_m[3], sj*sigma (boundary)            */
   int64_t g_off;    /* boundary only: offset into bc_g[] of Nqm^2 Dirichlet values, or -1 */
