@@ -1,0 +1,154 @@
+"""ctypes binding of the C ABI (include/d4est_b200.h) -- the same stub a d4est maintainer's
+Python tooling would use.  No compute happens in Python; there is no CPU
+fallback: loading fails loudly when libd4est_b200.so is missing, and every compute call
+fails with D4B_ENODEV when no CUDA device is present.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libd4est_b200.so")
+
+
+class D4BError(RuntimeError):
+    pass
+
+
+class HM(C.Structure):  # d4b_hm_t
+    _fields_ = [("nbr", C.c_int32), ("f_m", C.c_int8), ("f_p", C.c_int8), ("tcode", C.c_int8),
+                ("child_m", C.c_int8), ("child_p", C.c_int8), ("degq", C.c_int8),
+                ("face_slot", C.c_int8), ("pad", C.c_int8), ("pad0", C.c_int32),
+                ("fac_off", C.c_int64), ("g_off", C.c_int64), ("pad2", C.c_int64)]
+
+
+_P = C.c_void_p
+
+
+class MeshDesc(C.Structure):  # d4b_mesh_desc_t
+    _fields_ = [("n_local", C.c_int32), ("n_ghost", C.c_int32), ("quad_type", C.c_int32),
+                ("reserved", C.c_int32), ("deg", _P), ("node_off", _P), ("degq", _P), ("quad_off", _P),
+                ("G", _P), ("hm_begin", _P), ("hm", _P), ("fac", _P), ("n_fac", C.c_int64),
+                ("bc_g", _P), ("n_bc_g", C.c_int64), ("n_peers", C.c_int32), ("reserved2", C.c_int32),
+                ("peer_rank", _P), ("send_begin", _P), ("send_elem", _P), ("recv_begin", _P)]
+
+
+# every symbol include/d4est_b200.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "d4b_last_error": (C.c_char_p, []),
+    "d4b_version": (C.c_char_p, []),
+    "d4b_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "d4b_set_device": (C.c_int, [C.c_int]),
+    "d4b_mesh_create": (C.c_int, [C.POINTER(MeshDesc), C.POINTER(_P)]),
+    "d4b_mesh_destroy": (None, [_P]),
+    "d4b_mesh_local_nodes": (C.c_int64, [_P]),
+    "d4b_mesh_ghost_nodes": (C.c_int64, [_P]),
+    "d4b_mesh_bytes": (C.c_int64, [_P]),
+    "d4b_mesh_algorithmic_bytes": (C.c_int64, [_P]),
+    "d4b_apply_host": (C.c_int, [_P, _P, _P]),
+    "d4b_apply_dev": (C.c_int, [_P, _P, _P, _P]),
+    "d4b_set_ghost_host": (C.c_int, [_P, _P]),
+    "d4b_kernel_launches": (C.c_int64, []),
+    "d4b_dev_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
+    "d4b_dev_free": (C.c_int, [_P]),
+    "d4b_h2d": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "d4b_d2h": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "d4b_sync": (C.c_int, [_P]),
+    "d4b_host_alloc_pinned": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
+    "d4b_host_free_pinned": (C.c_int, [_P]),
+}
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise D4BError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU fallback)")
+        _lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(_lib, name)
+            fn.restype, fn.argtypes = res, args
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise D4BError(f"d4est_b200 error {rc}: {lib().d4b_last_error().decode()}")
+
+
+def _ptr(a):
+    return None if a is None or a.size == 0 else a.ctypes.data_as(_P)
+
+
+class MeshLevel:
+    """Device-resident mesh level built from flat tables (dict of numpy arrays with the field
+    names of d4b_mesh_desc_t, e.g. an oracle fixture or d4est_b200.brick.brick_tables())."""
+
+    def __init__(self, t):
+        L = lib()
+        nl, ng, qt, npeer = [int(v) for v in t["hdr"]]
+        self._keep = k = {}
+        def arr(name, dt):
+            a = np.ascontiguousarray(t.get(name, np.zeros(0, dt)))
+            if a.dtype != np.dtype(dt):
+                a = a.view(np.uint8) if name == "hm" else a.astype(dt)
+            k[name] = a
+            return a
+        d = MeshDesc()
+        d.n_local, d.n_ghost, d.quad_type, d.n_peers = nl, ng, qt, npeer
+        d.deg = _ptr(arr("deg", np.int32)); d.node_off = _ptr(arr("node_off", np.int64))
+        d.degq = _ptr(arr("degq", np.int32)); d.quad_off = _ptr(arr("quad_off", np.int64))
+        d.G = _ptr(arr("G", np.float64)); d.hm_begin = _ptr(arr("hm_begin", np.int32))
+        hm = np.ascontiguousarray(t["hm"]); k["hm"] = hm
+        d.hm = _ptr(hm.view(np.uint8))
+        fac = arr("fac", np.float64); d.fac = _ptr(fac); d.n_fac = fac.size
+        g = arr("bc_g", np.float64); d.bc_g = _ptr(g); d.n_bc_g = g.size
+        d.peer_rank = _ptr(arr("peer_rank", np.int32)); d.send_begin = _ptr(arr("send_begin", np.int32))
+        d.send_elem = _ptr(arr("send_elem", np.int32)); d.recv_begin = _ptr(arr("recv_begin", np.int32))
+        if k["send_begin"].size == 0:
+            k["send_begin"] = np.zeros(1, np.int32); d.send_begin = _ptr(k["send_begin"])
+            k["recv_begin"] = np.zeros(1, np.int32); d.recv_begin = _ptr(k["recv_begin"])
+        self.handle = _P()
+        check(L.d4b_mesh_create(C.byref(d), C.byref(self.handle)))
+        self.local_nodes = int(L.d4b_mesh_local_nodes(self.handle))
+        self.ghost_nodes = int(L.d4b_mesh_ghost_nodes(self.handle))
+        self.n_local = nl
+
+    @property
+    def algorithmic_bytes(self):
+        return int(lib().d4b_mesh_algorithmic_bytes(self.handle))
+
+    @property
+    def resident_bytes(self):
+        return int(lib().d4b_mesh_bytes(self.handle))
+
+    def set_ghost(self, ug):
+        ug = np.ascontiguousarray(ug, np.float64)
+        assert ug.size == self.ghost_nodes
+        check(lib().d4b_set_ghost_host(self.handle, _ptr(ug)))
+
+    def apply_host(self, u, out=None):
+        """Au = A u with HOST buffers (H2D + kernel + D2H): d4b_apply_host."""
+        u = np.ascontiguousarray(u, np.float64)
+        assert u.size == self.local_nodes
+        Au = np.empty_like(u) if out is None else out
+        check(lib().d4b_apply_host(self.handle, _ptr(u), Au.ctypes.data_as(_P)))
+        return Au
+
+    def apply_dev(self, u_ptr, Au_ptr, stream=0):
+        """Au = A u with DEVICE pointers (ints), on the given CUDA stream: d4b_apply_dev."""
+        check(lib().d4b_apply_dev(self.handle, _P(u_ptr), _P(Au_ptr), _P(stream)))
+
+    def close(self):
+        if self.handle:
+            lib().d4b_mesh_destroy(self.handle)
+            self.handle = _P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
