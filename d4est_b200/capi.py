@@ -33,6 +33,14 @@ class MeshDesc(C.Structure):  # d4b_mesh_desc_t
                 ("peer_rank", _P), ("send_begin", _P), ("send_elem", _P), ("recv_begin", _P)]
 
 
+class BrickParams(C.Structure):  # d4b_brick_params_t
+    _fields_ = [("nx", C.c_int32), ("ny", C.c_int32), ("nz", C.c_int32), ("deg", C.c_int32),
+                ("degq", C.c_int32), ("quad_type", C.c_int32),
+                ("x0", C.c_double), ("x1", C.c_double), ("y0", C.c_double), ("y1", C.c_double),
+                ("z0", C.c_double), ("z1", C.c_double), ("penalty_prefactor", C.c_double),
+                ("face_h", C.c_double)]
+
+
 # every symbol include/d4est_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "d4b_last_error": (C.c_char_p, []),
@@ -41,6 +49,7 @@ SYMBOLS = {
     "d4b_set_device": (C.c_int, [C.c_int]),
     "d4b_mesh_create": (C.c_int, [C.POINTER(MeshDesc), C.POINTER(_P)]),
     "d4b_mesh_destroy": (None, [_P]),
+    "d4b_brick_create": (C.c_int, [C.POINTER(BrickParams), C.POINTER(_P)]),
     "d4b_mesh_local_nodes": (C.c_int64, [_P]),
     "d4b_mesh_ghost_nodes": (C.c_int64, [_P]),
     "d4b_mesh_bytes": (C.c_int64, [_P]),
@@ -89,6 +98,9 @@ class MeshLevel:
 
     def __init__(self, t):
         L = lib()
+        self.handle = _P()
+        if t is None:
+            return
         nl, ng, qt, npeer = [int(v) for v in t["hdr"]]
         self._keep = k = {}
         def arr(name, dt):
@@ -116,6 +128,18 @@ class MeshLevel:
         self.local_nodes = int(L.d4b_mesh_local_nodes(self.handle))
         self.ghost_nodes = int(L.d4b_mesh_ghost_nodes(self.handle))
         self.n_local = nl
+
+    @classmethod
+    def brick(cls, n, deg=3, degq=None, quad_type=0, prefactor=2.0, box=(0., 1., 0., 1., 0., 1.), face_h=0.0):
+        """Synthetic uniform brick generated on the device (d4b_brick_create)."""
+        nx, ny, nz = (n, n, n) if np.isscalar(n) else n
+        p = BrickParams(nx, ny, nz, deg, deg if degq is None else degq, quad_type, *box, prefactor, face_h)
+        self = cls(None)
+        check(lib().d4b_brick_create(C.byref(p), C.byref(self.handle)))
+        self.local_nodes = int(lib().d4b_mesh_local_nodes(self.handle))
+        self.ghost_nodes = 0
+        self.n_local = nx * ny * nz
+        return self
 
     @property
     def algorithmic_bytes(self):

@@ -90,7 +90,7 @@ template <class T> static int upload(T **dst, const T *src, size_t n, int64_t *b
 {
   *dst = nullptr;
   D4B_CUDA(cudaMalloc((void **)dst, (n ? n : 1) * sizeof(T)));
-  if (n) D4B_CUDA(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+  if (n && src) D4B_CUDA(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice)); /* src NULL: filled on device */
   *bytes += (int64_t)(n * sizeof(T));
   return D4B_OK;
 }
@@ -125,7 +125,7 @@ int d4b_mesh_create(const d4b_mesh_desc_t *D, d4b_mesh_t **out)
     int64_t N = D->deg[e] + 1, Nq = D->degq[e] + 1;
     alg += 16 * N * N * N + 48 * Nq * Nq * Nq;
   }
-  for (int64_t r = 0; r < m->n_hm; r++) {
+  for (int64_t r = 0; D->hm && r < m->n_hm; r++) {
     const d4b_hm_t &h = D->hm[r];
     if (h.degq > D4B_MAX_DEGQ || h.nbr >= ne || h.f_m < 0 || h.f_m > 5) { d4b_set_error("bad half-mortar %lld", (long long)r); free(m); return D4B_EINVAL; }
     if (h.degq > m->max_degq) m->max_degq = h.degq;

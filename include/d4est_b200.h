@@ -111,6 +111,22 @@ int64_t d4b_mesh_ghost_nodes(const d4b_mesh_t *m);
 int64_t d4b_mesh_bytes(const d4b_mesh_t *m);          /* HBM footprint of the level    */
 int64_t d4b_mesh_algorithmic_bytes(const d4b_mesh_t *m); /* SURVEY 8(d) bytes per apply */
 
+/* Synthetic uniform brick (BASELINE config 2: "Poisson on a uniform brick mesh, single degree"),
+ * generated DIRECTLY into the resident tables by CUDA kernels -- same tables the glue produces
+ * from the reference's [geometry] name = brick (Geometry/d4est_geometry_brick.c:121,152) with
+ * face_h_type = FACE_H_EQ_TREE_H (Mesh/d4est_mesh.c:717-726), penalty maxp_sqr_over_minh
+ * (dGMath/d4est_laplacian_with_opt_flux_sipg.c:1314) and homogeneous Dirichlet data.  Elements are
+ * in Morton order (p4est's order inside one tree when nx = ny = nz = 2^level). */
+typedef struct d4b_brick_params {
+  int32_t nx, ny, nz;       /* elements per direction                                   */
+  int32_t deg, degq;        /* uniform degree and quadrature degree                     */
+  int32_t quad_type;        /* D4B_QUAD_*                                               */
+  double x0, x1, y0, y1, z0, z1;
+  double penalty_prefactor; /* [flux] sipg_penalty_prefactor                            */
+  double face_h;            /* h in the penalty; <= 0 means 1/nx (= dq/ROOT_LEN)        */
+} d4b_brick_params_t;
+int d4b_brick_create(const d4b_brick_params_t *p, d4b_mesh_t **out);
+
 /* ---- operator apply: replaces d4est_laplacian_with_opt_apply_aij
  *      (dGMath/d4est_laplacian_with_opt.c:289) and its twin d4est_laplacian_apply_aij
  *      (dGMath/d4est_laplacian.c:317).  Au is overwritten.                            */
