@@ -7,6 +7,7 @@
 #include <cstring>
 #include <vector>
 #include <atomic>
+#include <algorithm>
 
 static thread_local char g_err[512] = "";
 static std::atomic<long long> g_launches{0};
@@ -171,6 +172,7 @@ int d4b_mesh_create(const d4b_mesh_desc_t *D, d4b_mesh_t **out)
     if ((rc = upload(&m->send_elem, D->send_elem, (size_t)D->send_begin[np], &dummy)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
     D4B_CUDA(cudaMalloc((void **)&m->send_buf, (sn ? sn : 1) * sizeof(double)));
   }
+  if ((rc = d4b_fast_classify(m, D)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
   *out = m;
   return D4B_OK;
 }
@@ -181,6 +183,8 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   cudaFree(m->deg); cudaFree(m->node_off); cudaFree(m->degq); cudaFree(m->quad_off); cudaFree(m->G);
   cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost);
   cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->send_elem); cudaFree(m->send_buf);
+  for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); }
+  cudaFree(m->generic_list);
   free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
   free(m->send_node_begin_h); free(m->recv_node_begin_h);
   if (m->stream) cudaStreamDestroy(m->stream);
@@ -204,7 +208,6 @@ int d4b_apply_dev(d4b_mesh_t *m, const double *u, double *Au, void *stream)
   int handled = 0;
   int rc = d4b_launch_fast(m, u, Au, st, &handled);
   if (rc != D4B_OK) return rc;
-  if (!handled) rc = d4b_launch_generic(m, u, Au, nullptr, 0, st);
   return rc;
 }
 
@@ -225,7 +228,45 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
 
 } /* extern C */
 
-/* fast templated kernels are added in d4b_apply_fast.cu; until an element class has one
- * the generic kernel handles it */
-__attribute__((weak)) int d4b_launch_fast(const d4b_mesh *, const double *, double *, cudaStream_t, int *handled)
-{ *handled = 0; return D4B_OK; }
+/* Split the local elements into degree buckets of "regular" elements (every face conforming with
+ * an equal-degree neighbour, or a boundary) and the rest (generic kernel). */
+int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
+{
+  const int nl = m->n_local;
+  std::vector<std::vector<int32_t>> el(D4B_NDEG * D4B_NDEGQ), fr(D4B_NDEG * D4B_NDEGQ);
+  std::vector<int32_t> gen;
+  const bool off = getenv("D4B_NO_FAST") != nullptr;
+  for (int e = 0; e < nl; e++) {
+    int dg = D->deg[e], dq = D->degq[e];
+    bool ok = !off && d4b_fast_supported(dg + 1, dq + 1);
+    int32_t rec[6] = {-1, -1, -1, -1, -1, -1};
+    if (ok && D->hm) {
+      if (D->hm_begin[e + 1] - D->hm_begin[e] != 6) ok = false;
+      for (int r = D->hm_begin[e]; ok && r < D->hm_begin[e + 1]; r++) {
+        const d4b_hm_t &h = D->hm[r];
+        if (h.child_m >= 0 || h.child_p >= 0 || h.degq != dq || rec[h.f_m] >= 0) { ok = false; break; }
+        if (h.nbr >= 0 && D->deg[h.nbr] != dg) { ok = false; break; }
+        rec[h.f_m] = r;
+      }
+    } else if (ok) {
+      for (int f = 0; f < 6; f++) rec[f] = 6 * e + f; /* device-built brick: records in face order */
+    }
+    if (!ok) { gen.push_back(e); continue; }
+    int k = dg * D4B_NDEGQ + dq;
+    el[k].push_back(e); fr[k].insert(fr[k].end(), rec, rec + 6);
+  }
+  m->n_fast = 0;
+  int64_t dummy = 0; int rc;
+  for (int k = 0; k < D4B_NDEG * D4B_NDEGQ; k++) {
+    if (el[k].empty()) continue;
+    if (m->n_fast == D4B_MAX_BUCKETS) { gen.insert(gen.end(), el[k].begin(), el[k].end()); continue; }
+    d4b_fast_bucket &b = m->fast[m->n_fast++];
+    b.N = k / D4B_NDEGQ + 1; b.Nq = k % D4B_NDEGQ + 1; b.count = (int)el[k].size();
+    if ((rc = upload(&b.elem_list, el[k].data(), el[k].size(), &dummy)) != D4B_OK) return rc;
+    if ((rc = upload(&b.frec, fr[k].data(), fr[k].size(), &dummy)) != D4B_OK) return rc;
+  }
+  m->n_generic = (int)gen.size();
+  std::sort(gen.begin(), gen.end());
+  if ((rc = upload(&m->generic_list, gen.data(), gen.size(), &dummy)) != D4B_OK) return rc;
+  return D4B_OK;
+}

@@ -21,6 +21,14 @@ struct d4b_ops_dev {
   const double *pool;              /* device pointer */
 };
 
+/* one degree bucket of "regular" elements handled by a templated kernel (d4b_apply_fast.cu) */
+struct d4b_fast_bucket {
+  int N, Nq, count;
+  int32_t *elem_list;   /* device: element ids                                          */
+  int32_t *frec;        /* device: [count][6] half-mortar record index of face f        */
+};
+#define D4B_MAX_BUCKETS 32
+
 /* device-resident mesh level */
 struct d4b_mesh {
   int n_local, n_ghost, quad_type, max_deg, max_degq, max_deg_ext;
@@ -35,11 +43,16 @@ struct d4b_mesh {
   int n_peers; int32_t *peer_rank_h, *send_begin_h, *recv_begin_h; int32_t *send_elem;
   int64_t *send_node_begin_h, *recv_node_begin_h; double *send_buf; int64_t send_nodes;
   cudaStream_t stream;
+  d4b_fast_bucket fast[D4B_MAX_BUCKETS]; int n_fast;
+  int32_t *generic_list; int n_generic;   /* elements left to the generic kernel */
 };
 
 void d4b_set_error(const char *fmt, ...);
 const d4b_ops_dev *d4b_ops_device(int quad_type); /* lazily built + uploaded */
 void d4b_count_launch(int n);
+bool d4b_fast_supported(int N, int Nq);
+/* split elements into fast buckets + generic list; D->hm == NULL means the uniform device-built brick */
+int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D);
 
 #define D4B_CUDA(call)                                                                   \
   do { cudaError_t e_ = (call);                                                          \
