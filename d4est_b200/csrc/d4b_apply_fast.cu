@@ -63,25 +63,29 @@ template <int n> __device__ __forceinline__ void st(double *p, int s, const doub
 }
 
 template <int N, int Nq> struct FL {
-  static constexpr int M = N > Nq ? N : Nq;
   static constexpr int N2 = N * N, N3 = N * N * N, Q2 = Nq * Nq, Q3 = Nq * Nq * Nq, NQ = N * Nq;
-  static constexpr int VB = M * M * M;
-  static constexpr int TR = 4 * 2 * N2, S1 = 4 * 3 * NQ, QV = 4 * 4 * Q2, FH = 2 * 4 * Q2, R1 = 2 * 3 * NQ, R2 = 2 * 2 * N2;
-  static constexpr int RA = TR > QV ? TR : QV, RB = S1 > FH ? S1 : FH;
-  static constexpr int FACE = RA + RB + R1 + R2;
-  static constexpr int SCR = 6 * VB > FACE ? 6 * VB : FACE;
-  static constexpr int PER = 2 * N3 + SCR;          /* doubles of shared memory per element */
-  static constexpr int TPE = N2;                     /* threads per element */
+  /* shared-memory strides chosen so that the 16 lanes of one element (N = 4) hit distinct banks */
+  static constexpr int SJ = N + 1, SK = N * (N + 1), UA = N * SK;        /* U, ACC: (i,j,k) -> i + SJ j + SK k */
+  static constexpr int AS = N2 + (N == 4 ? 4 : 0), AB = Nq * AS;          /* A bufs: (i,j,c) -> i + N j + AS c  */
+  static constexpr int BS = NQ + 1, BB = Nq * BS;                         /* B bufs: (i,b,c) -> i + BS b + N c  */
+  static constexpr int VOL = 2 * AB + 3 * BB;
+  static constexpr int TB = N2 + 1;                                       /* trace block stride */
+  static constexpr int TR = 8 * TB, QV = 4 * 2 * Q2, R1 = 2 * 3 * NQ;
+  static constexpr int S1 = 4 * 3 * NQ, FH = 2 * 4 * Q2, R2 = 2 * 2 * N2;
+  static constexpr int RA = (TR > QV ? (TR > R1 ? TR : R1) : (QV > R1 ? QV : R1));
+  static constexpr int RB = (S1 > FH ? (S1 > R2 ? S1 : R2) : (FH > R2 ? FH : R2));
+  static constexpr int FACE = RA + RB;
+  static constexpr int SCR = VOL > FACE ? VOL : FACE;
+  static constexpr int PER = 2 * UA + SCR;           /* doubles of shared memory per element */
+  static constexpr int TPE = N2;                      /* threads per element */
   static constexpr int EPB = (128 / TPE) > 0 ? (128 / TPE) : 1; /* elements per CTA */
   static constexpr int THREADS = TPE * EPB;
 };
 
-__device__ __forceinline__ int f_tsrc(int tcode, int n, int a, int b)
+/* face-local axis strides for direction d in an (i,j,k) array with strides (1, sj, sk) */
+__device__ __forceinline__ void face_strides(int d, int sj, int sk, int &sa, int &sb, int &sn)
 {
-  int x = (tcode & 1) ? a : b, y = (tcode & 1) ? b : a;
-  if (tcode & 2) x = n - 1 - x;
-  if (tcode & 4) y = n - 1 - y;
-  return x + n * y;
+  sa = d == 0 ? sj : 1; sb = d == 2 ? sj : sk; sn = d == 0 ? 1 : (d == 1 ? sj : sk);
 }
 
 template <int N, int Nq>
@@ -89,64 +93,92 @@ __global__ void __launch_bounds__(FL<N, Nq>::THREADS)
 d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
 {
   using L = FL<N, Nq>;
-  constexpr int N2 = L::N2, N3 = L::N3, Q2 = L::Q2, Q3 = L::Q3, NQ = L::NQ, VB = L::VB, TPE = L::TPE;
+  constexpr int N2 = L::N2, N3 = L::N3, Q2 = L::Q2, Q3 = L::Q3, NQ = L::NQ, TPE = L::TPE;
+  constexpr int SJ = L::SJ, SK = L::SK, AS = L::AS, BS = L::BS, TB = L::TB;
   extern __shared__ double sm[];
   const int le = threadIdx.x / TPE, lt = threadIdx.x % TPE;
   const int slot = blockIdx.x * L::EPB + le;
   const bool active = slot < A.n_list;
   const int e = active ? A.elem_list[slot] : 0;
-  double *U = sm + le * L::PER, *ACC = U + N3, *S = ACC + N3;
-  double *V0 = S, *V1 = S + VB, *V2 = S + 2 * VB, *V3 = S + 3 * VB, *V4 = S + 4 * VB, *V5 = S + 5 * VB;
+  double *U = sm + le * L::PER, *ACC = U + L::UA, *S = ACC + L::UA;
+  double *V0 = S, *V1 = S + L::AB, *V2 = S + 2 * L::AB, *V3 = V2 + L::BB, *V4 = V3 + L::BB;
   const double *B = c_ft.B, *C = c_ft.C, *D = c_ft.D;
   const double *ue = A.u + A.node_off[e];
+  const int32_t *fr = frec + 6 * (active ? slot : 0);
+  const int fa = lt % N, fb = lt / N; /* my face node (T stage) */
 
-  if (active)
+  /* neighbour normal lines of direction d, prefetched into registers one direction ahead */
+  double xn[2][N];
+  int nlay[2];
+  auto prefetch = [&](int d) {
 #pragma unroll
-    for (int m = 0; m < N3 / TPE; m++) U[lt + TPE * m] = ue[lt + TPE * m];
+    for (int s = 0; s < 2; s++) {
+      const d4b_hm_t *h = A.hm + fr[2 * d + s];
+      int nb = h->nbr; nlay[s] = -1;
+      if (nb >= 0) {
+        const double *un = (nb < A.n_local) ? A.u + A.node_off[nb] : A.u_ghost + (A.node_off[nb] - A.local_nodes);
+        int fp = h->f_p, dp = fp >> 1; nlay[s] = (fp & 1) ? N - 1 : 0;
+        int pa, pb, pn; face_strides(dp, N, N2, pa, pb, pn);
+        const double *p = un + fa * pa + fb * pb;
+#pragma unroll
+        for (int m = 0; m < N; m++) xn[s][m] = __ldg(p + m * pn);
+      }
+    }
+  };
+  if (active) {
+    prefetch(0);
+#pragma unroll
+    for (int m = 0; m < N3 / TPE; m++) { /* g = lt + TPE m = (i,j) + N2 k */
+      U[(lt % N) + SJ * (lt / N) + SK * m] = ue[lt + TPE * m];
+    }
+  }
   __syncthreads();
 
   /* ---------------- volume (Quadrature/d4est_quadrature.c:263-375, sum-factorised) */
-  if (active) { /* along t: lines (i,j) */
-    for (int t = lt; t < N2; t += TPE) {
-      double x[N], y[Nq];
-      ld<N>(U + t, N2, x);
-      mat1<N, Nq, false>(B, x, y); st<Nq>(V0 + t, N2, y);
-      mat1<N, Nq, false>(C, x, y); st<Nq>(V1 + t, N2, y);
-    }
+  if (active) { /* along t: line (i,j) */
+    const int i = lt % N, j = lt / N;
+    double x[N], y[Nq];
+    ld<N>(U + i + SJ * j, SK, x);
+    mat1<N, Nq, false>(B, x, y); st<Nq>(V0 + lt, AS, y);
+    mat1<N, Nq, false>(C, x, y); st<Nq>(V1 + lt, AS, y);
   }
   __syncthreads();
   if (active) { /* along s: lines (i,c) */
     for (int t = lt; t < NQ; t += TPE) {
       int i = t % N, c = t / N;
       double x[N], y[Nq];
-      ld<N>(V0 + i + N2 * c, N, x);
-      mat1<N, Nq, false>(B, x, y); st<Nq>(V2 + i + NQ * c, N, y);
-      mat1<N, Nq, false>(C, x, y); st<Nq>(V3 + i + NQ * c, N, y);
-      ld<N>(V1 + i + N2 * c, N, x);
-      mat1<N, Nq, false>(B, x, y); st<Nq>(V4 + i + NQ * c, N, y);
+      ld<N>(V0 + i + AS * c, N, x);
+      mat1<N, Nq, false>(B, x, y); st<Nq>(V2 + i + N * c, BS, y);
+      mat1<N, Nq, false>(C, x, y); st<Nq>(V3 + i + N * c, BS, y);
+      ld<N>(V1 + i + AS * c, N, x);
+      mat1<N, Nq, false>(B, x, y); st<Nq>(V4 + i + N * c, BS, y);
     }
   }
   __syncthreads();
-  if (active) { /* along r: lines (b,c); metric; transposed r-contraction, all in registers */
+  if (active) { /* along r: lines (b,c); metric; transposed r-contraction; in place, in registers */
     const double *Ge = A.G + 6 * A.quad_off[e];
     for (int t = lt; t < Q2; t += TPE) {
+      int b = t % Nq, c = t / Nq;
+      double Gv[6][Nq];
+#pragma unroll
+      for (int k = 0; k < 6; k++)
+#pragma unroll
+        for (int a = 0; a < Nq; a++) Gv[k][a] = __ldg(Ge + k * Q3 + Nq * t + a);
       double x[N], gr[Nq], gs[Nq], gt[Nq];
-      ld<N>(V2 + N * t, 1, x); mat1<N, Nq, false>(C, x, gr);
-      ld<N>(V3 + N * t, 1, x); mat1<N, Nq, false>(B, x, gs);
-      ld<N>(V4 + N * t, 1, x); mat1<N, Nq, false>(B, x, gt);
-      const double *Gq = Ge + Nq * t;
+      const int o = BS * b + N * c;
+      ld<N>(V2 + o, 1, x); mat1<N, Nq, false>(C, x, gr);
+      ld<N>(V3 + o, 1, x); mat1<N, Nq, false>(B, x, gs);
+      ld<N>(V4 + o, 1, x); mat1<N, Nq, false>(B, x, gt);
 #pragma unroll
       for (int a = 0; a < Nq; a++) {
-        double G00 = Gq[a], G01 = Gq[Q3 + a], G02 = Gq[2 * Q3 + a], G11 = Gq[3 * Q3 + a],
-               G12 = Gq[4 * Q3 + a], G22 = Gq[5 * Q3 + a];
         double g0 = gr[a], g1 = gs[a], g2 = gt[a];
-        gr[a] = G00 * g0 + G01 * g1 + G02 * g2;
-        gs[a] = G01 * g0 + G11 * g1 + G12 * g2;
-        gt[a] = G02 * g0 + G12 * g1 + G22 * g2;
+        gr[a] = Gv[0][a] * g0 + Gv[1][a] * g1 + Gv[2][a] * g2;
+        gs[a] = Gv[1][a] * g0 + Gv[3][a] * g1 + Gv[4][a] * g2;
+        gt[a] = Gv[2][a] * g0 + Gv[4][a] * g1 + Gv[5][a] * g2;
       }
-      mat1<Nq, N, true>(C, gr, x); st<N>(V0 + N * t, 1, x);
-      mat1<Nq, N, true>(B, gs, x); st<N>(V1 + N * t, 1, x);
-      mat1<Nq, N, true>(B, gt, x); st<N>(V5 + N * t, 1, x);
+      mat1<Nq, N, true>(C, gr, x); st<N>(V2 + o, 1, x);
+      mat1<Nq, N, true>(B, gs, x); st<N>(V3 + o, 1, x);
+      mat1<Nq, N, true>(B, gt, x); st<N>(V4 + o, 1, x);
     }
   }
   __syncthreads();
@@ -154,67 +186,58 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
     for (int t = lt; t < NQ; t += TPE) {
       int i = t % N, c = t / N;
       double x[Nq], y[N];
-      ld<Nq>(V0 + i + NQ * c, N, x); mat1<Nq, N, true>(B, x, y);
-      ld<Nq>(V1 + i + NQ * c, N, x); mat1_acc<Nq, N, true>(C, x, y);
-      st<N>(V2 + i + N2 * c, N, y);
-      ld<Nq>(V5 + i + NQ * c, N, x); mat1<Nq, N, true>(B, x, y);
-      st<N>(V3 + i + N2 * c, N, y);
+      ld<Nq>(V2 + i + N * c, BS, x); mat1<Nq, N, true>(B, x, y);
+      ld<Nq>(V3 + i + N * c, BS, x); mat1_acc<Nq, N, true>(C, x, y);
+      st<N>(V0 + i + AS * c, N, y);
+      ld<Nq>(V4 + i + N * c, BS, x); mat1<Nq, N, true>(B, x, y);
+      st<N>(V1 + i + AS * c, N, y);
     }
   }
   __syncthreads();
-  if (active) { /* transposed t-contraction: lines (i,j) -> ACC */
-    for (int t = lt; t < N2; t += TPE) {
-      double x[Nq], y[N];
-      ld<Nq>(V2 + t, N2, x); mat1<Nq, N, true>(B, x, y);
-      ld<Nq>(V3 + t, N2, x); mat1_acc<Nq, N, true>(C, x, y);
-      st<N>(ACC + t, N2, y);
-    }
+  if (active) { /* transposed t-contraction: line (i,j) -> ACC */
+    const int i = lt % N, j = lt / N;
+    double x[Nq], y[N];
+    ld<Nq>(V0 + lt, AS, x); mat1<Nq, N, true>(B, x, y);
+    ld<Nq>(V1 + lt, AS, x); mat1_acc<Nq, N, true>(C, x, y);
+    st<N>(ACC + i + SJ * j, SK, y);
   }
   __syncthreads();
 
   /* ---------------- faces, one direction (2 own faces + their 2 neighbours) at a time */
-  double *RA = S, *RB = S + L::RA, *RC = RB + L::RB, *RD = RC + L::R1;
-  const int32_t *fr = frec + 6 * (active ? slot : 0);
+  double *RA = S, *RB = S + L::RA;
 #pragma unroll 1
   for (int d = 0; d < 3; d++) {
-    const int sa = d == 0 ? N : 1, sb = d == 2 ? N : N2, sn = d == 0 ? 1 : (d == 1 ? N : N2);
-    const int la = d == 0 ? 1 : 0, lb = d == 2 ? 1 : 2;
-    /* T: traces u and du/dn on the face nodes: [side][u,dn][a + N b]; sides: own0 own1 nbr0 nbr1 */
+    int sa, sb, sn; face_strides(d, SJ, SK, sa, sb, sn);
+    /* T: traces u and du/dn at my face node: RA[(side*2 + fld)*TB + a + N b]; sides own0 own1 nbr0 nbr1 */
     if (active) {
-      for (int t = lt; t < 3 * N2; t += TPE) {
-        int which = t / N2, ab = t % N2, a = ab % N, b = ab / N;
-        double x[N];
-        if (which == 0) {
-          ld<N>(U + a * sa + b * sb, sn, x);
-          double d0 = 0., d1 = 0.;
+      double x[N];
+      ld<N>(U + fa * sa + fb * sb, sn, x);
+      double d0 = 0., d1 = 0.;
 #pragma unroll
-          for (int m = 0; m < N; m++) { d0 = fma(D[m], x[m], d0); d1 = fma(D[(N - 1) * N + m], x[m], d1); }
-          RA[ab] = x[0]; RA[N2 + ab] = d0; RA[2 * N2 + ab] = x[N - 1]; RA[3 * N2 + ab] = d1;
-        } else {
-          const d4b_hm_t *h = A.hm + fr[2 * d + which - 1];
-          int nb = h->nbr;
-          if (nb >= 0) {
-            const double *un = (nb < A.n_local) ? A.u + A.node_off[nb] : A.u_ghost + (A.node_off[nb] - A.local_nodes);
-            int fp = h->f_p, dp = fp >> 1, lay = (fp & 1) ? N - 1 : 0;
-            int pa = dp == 0 ? N : 1, pb = dp == 2 ? N : N2, pn = dp == 0 ? 1 : (dp == 1 ? N : N2);
-            const double *p = un + a * pa + b * pb;
-            double dn = 0.;
+      for (int m = 0; m < N; m++) { d0 = fma(D[m], x[m], d0); d1 = fma(D[(N - 1) * N + m], x[m], d1); }
+      RA[lt] = x[0]; RA[TB + lt] = d0; RA[2 * TB + lt] = x[N - 1]; RA[3 * TB + lt] = d1;
 #pragma unroll
-            for (int m = 0; m < N; m++) { x[m] = __ldg(p + m * pn); dn = fma(D[lay * N + m], x[m], dn); }
-            double *T = RA + (which + 1) * 2 * N2;
-            T[ab] = (fp & 1) ? x[N - 1] : x[0]; T[N2 + ab] = dn;
-          }
+      for (int s = 0; s < 2; s++) {
+        if (nlay[s] >= 0) {
+          double dn = 0.;
+          const double *Dr = D + nlay[s] * N;
+#pragma unroll
+          for (int m = 0; m < N; m++) dn = fma(Dr[m], xn[s][m], dn);
+          RA[(4 + 2 * s) * TB + lt] = nlay[s] ? xn[s][N - 1] : xn[s][0];
+          RA[(5 + 2 * s) * TB + lt] = dn;
         }
       }
     }
+    const bool nbnd0 = active && nlay[0] < 0, nbnd1 = active && nlay[1] < 0; /* boundary flags of this direction */
+    if (active && d < 2) prefetch(d + 1);
     __syncthreads();
-    /* S1: contraction along face axis a: [side][uB,uC,dnB][qa + Nq b] */
+    /* S1: contraction along face axis a: RB[(side*3 + {uB,uC,dnB})*NQ + qa + Nq b] */
     if (active) {
       for (int t = lt; t < 8 * N; t += TPE) {
         int b = t % N, fld = (t / N) & 1, side = t / (2 * N);
-        if (side >= 2 && A.hm[fr[2 * d + side - 2]].nbr < 0) continue;
+        if ((side == 2 && nbnd0) || (side == 3 && nbnd1)) continue;
         double x[N], y[Nq];
-        ld<N>(RA + (side * 2 + fld) * N2 + N * b, 1, x);
+        ld<N>(RA + (side * 2 + fld) * TB + N * b, 1, x);
         double *o = RB + side * 3 * NQ + Nq * b;
         if (fld == 0) {
           mat1<N, Nq, false>(B, x, y); st<Nq>(o, 1, y);
@@ -225,54 +248,70 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
       }
     }
     __syncthreads();
-    /* QV: contraction along face axis b: [side][u, du/da, du/db, du/dn][qa + Nq qb] */
+    /* QV: contraction along face axis b, then fold the gradient with the face factors:
+     * RA[(side*2 + 0)*Q2 + q] = u,  RA[(side*2 + 1)*Q2 + q] = sum_l a_l du/dr_l  (q in MY point order) */
     if (active) {
-      for (int t = lt; t < 12 * Nq; t += TPE) {
-        int qa = t % Nq, fld = (t / Nq) % 3, side = t / (3 * Nq);
-        if (side >= 2 && A.hm[fr[2 * d + side - 2]].nbr < 0) continue;
-        double x[N], y[Nq];
-        ld<N>(RB + (side * 3 + fld) * NQ + qa, Nq, x);
-        double *o = RA + side * 4 * Q2 + qa;
-        if (fld == 0) {
-          mat1<N, Nq, false>(B, x, y); st<Nq>(o, Nq, y);
-          mat1<N, Nq, false>(C, x, y); st<Nq>(o + 2 * Q2, Nq, y);
+      for (int t = lt; t < 4 * Nq; t += TPE) {
+        int qa = t % Nq, side = t / Nq, s = side & 1;
+        if ((side == 2 && nbnd0) || (side == 3 && nbnd1)) continue;
+        const d4b_hm_t *h = A.hm + fr[2 * d + s];
+        const double *F = A.fac + h->fac_off;
+        const double *in = RB + side * 3 * NQ + qa;
+        double x[N], u[Nq], ua[Nq], ub[Nq], un[Nq];
+        ld<N>(in, Nq, x); mat1<N, Nq, false>(B, x, u); mat1<N, Nq, false>(C, x, ub);
+        ld<N>(in + NQ, Nq, x); mat1<N, Nq, false>(B, x, ua);
+        ld<N>(in + 2 * NQ, Nq, x); mat1<N, Nq, false>(B, x, un);
+        double *o = RA + side * 2 * Q2;
+        if (side < 2) {
+          const int ia = d == 0 ? 1 : 0, ib = d == 2 ? 1 : 2;
+#pragma unroll
+          for (int qb = 0; qb < Nq; qb++) {
+            int q = qa + Nq * qb;
+            o[q] = u[qb];
+            o[Q2 + q] = F[ia * Q2 + q] * ua[qb] + F[ib * Q2 + q] * ub[qb] + F[d * Q2 + q] * un[qb];
+          }
         } else {
-          mat1<N, Nq, false>(B, x, y); st<Nq>(o + (fld == 1 ? 1 : 3) * Q2, Nq, y);
+          const int tc = h->tcode, dp = h->f_p >> 1;
+          const int ia = dp == 0 ? 1 : 0, ib = dp == 2 ? 1 : 2;
+#pragma unroll
+          for (int qb = 0; qb < Nq; qb++) { /* (qa,qb) is the neighbour's point; find mine */
+            int xx = (tc & 2) ? Nq - 1 - qa : qa, yy = (tc & 4) ? Nq - 1 - qb : qb;
+            int q = (tc & 1) ? xx + Nq * yy : yy + Nq * xx;
+            o[q] = u[qb];
+            o[Q2 + q] = F[(3 + ia) * Q2 + q] * ua[qb] + F[(3 + ib) * Q2 + q] * ub[qb] + F[(3 + dp) * Q2 + q] * un[qb];
+          }
         }
       }
     }
     __syncthreads();
     /* FLUX at mortar quadrature points (…_flux_sipg.c:645-677 interior, :139-191 Dirichlet):
-     * FH[face][F, Ha, Hb, Hn][q] */
+     * RB[(face*4 + {F,Ha,Hb,Hn})*Q2 + q] */
     if (active) {
       for (int t = lt; t < 2 * Q2; t += TPE) {
         int s = t / Q2, q = t % Q2, qa = q % Nq, qb = q / Nq;
         const d4b_hm_t *h = A.hm + fr[2 * d + s];
         const double *F = A.fac + h->fac_off;
-        const double *o = RA + s * 4 * Q2;
+        const bool bnd = s ? nbnd1 : nbnd0;
+        double am0 = F[q], am1 = F[Q2 + q], am2 = F[2 * Q2 + q], sjs = F[(bnd ? 3 : 6) * Q2 + q];
         double w = c_ft.w[qa] * c_ft.w[qb];
-        double am[3] = { F[q], F[Q2 + q], F[2 * Q2 + q] };
-        double um = o[q];
-        double qm = am[la] * o[Q2 + q] + am[lb] * o[2 * Q2 + q] + am[d] * o[3 * Q2 + q];
-        double jump, t1, sjs, hs;
-        int nb = h->nbr;
-        if (nb >= 0) {
-          int src = f_tsrc(h->tcode, Nq, qa, qb), dp = h->f_p >> 1;
-          int pla = dp == 0 ? 1 : 0, plb = dp == 2 ? 1 : 2;
-          const double *p = RA + (2 + s) * 4 * Q2 + src;
-          double qp = F[(3 + pla) * Q2 + q] * p[Q2] + F[(3 + plb) * Q2 + q] * p[2 * Q2] + F[(3 + dp) * Q2 + q] * p[3 * Q2];
-          jump = um - p[0]; t1 = -0.5 * (qm + qp); sjs = F[6 * Q2 + q]; hs = -0.5;
+        double um = RA[s * 2 * Q2 + q], qm = RA[(s * 2 + 1) * Q2 + q];
+        double jump, t1, hs;
+        if (!bnd) {
+          jump = um - RA[(4 + 2 * s) * Q2 + q]; t1 = -0.5 * (qm + RA[(5 + 2 * s) * Q2 + q]); hs = -0.5;
         } else {
           double g = (h->g_off >= 0) ? A.bc_g[h->g_off + q] : 0.;
-          jump = um - g; t1 = -qm; sjs = F[3 * Q2 + q]; hs = -1.0;
+          jump = um - g; t1 = -qm; hs = -1.0;
         }
         double *fh = RB + s * 4 * Q2 + q;
         double wj = w * hs * jump;
-        fh[0] = w * (t1 + sjs * jump); fh[Q2] = wj * am[la]; fh[2 * Q2] = wj * am[lb]; fh[3 * Q2] = wj * am[d];
+        fh[0] = w * (t1 + sjs * jump);
+        fh[Q2] = wj * (d == 0 ? am1 : am0);
+        fh[2 * Q2] = wj * (d == 2 ? am1 : am2);
+        fh[3 * Q2] = wj * (d == 0 ? am0 : (d == 1 ? am1 : am2));
       }
     }
     __syncthreads();
-    /* BACK1: transposed contraction along b: R1[face][X1, Ha1, Hn1][qa + Nq b'] */
+    /* BACK1: transposed contraction along b: RA[(face*3 + {X1,Ha1,Hn1})*NQ + qa + Nq b'] */
     if (active) {
       for (int t = lt; t < 6 * Nq; t += TPE) {
         int qa = t % Nq, k = (t / Nq) % 3, s = t / (3 * Nq);
@@ -284,15 +323,15 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
         } else {
           ld<Nq>(fh + (k == 1 ? 1 : 3) * Q2, Nq, x); mat1<Nq, N, true>(B, x, y);
         }
-        st<N>(RC + (s * 3 + k) * NQ + qa, Nq, y);
+        st<N>(RA + (s * 3 + k) * NQ + qa, Nq, y);
       }
     }
     __syncthreads();
-    /* BACK2: transposed contraction along a: R2[face][Y, Z][a' + N b'] */
+    /* BACK2: transposed contraction along a: RB[(face*2 + {Y,Z})*N2 + a' + N b'] */
     if (active) {
       for (int t = lt; t < 4 * N; t += TPE) {
         int b = t % N, k = (t / N) & 1, s = t / (2 * N);
-        const double *r1 = RC + s * 3 * NQ + Nq * b;
+        const double *r1 = RA + s * 3 * NQ + Nq * b;
         double x[Nq], y[N];
         if (k == 0) {
           ld<Nq>(r1, 1, x); mat1<Nq, N, true>(B, x, y);
@@ -300,32 +339,28 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
         } else {
           ld<Nq>(r1 + 2 * NQ, 1, x); mat1<Nq, N, true>(B, x, y);
         }
-        st<N>(RD + (s * 2 + k) * N2 + N * b, 1, y);
+        st<N>(RB + (s * 2 + k) * N2 + N * b, 1, y);
       }
     }
     __syncthreads();
     /* LIFT (…_flux_sipg.c:918-958): face layer += Y, normal line += D[layer,:] Z */
     if (active) {
-      for (int t = lt; t < N2; t += TPE) {
-        int a = t % N, b = t / N;
-        double *acc = ACC + a * sa + b * sb;
-        double y0 = RD[t], z0 = RD[N2 + t], y1 = RD[2 * N2 + t], z1 = RD[3 * N2 + t];
+      double *acc = ACC + fa * sa + fb * sb;
+      double y0 = RB[lt], z0 = RB[N2 + lt], y1 = RB[2 * N2 + lt], z1 = RB[3 * N2 + lt];
 #pragma unroll
-        for (int m = 0; m < N; m++) {
-          double v = acc[m * sn] + D[m] * z0 + D[(N - 1) * N + m] * z1;
-          if (m == 0) v += y0;
-          if (m == N - 1) v += y1;
-          acc[m * sn] = v;
-        }
+      for (int m = 0; m < N; m++) {
+        double v = acc[m * sn] + D[m] * z0 + D[(N - 1) * N + m] * z1;
+        if (m == 0) v += y0;
+        if (m == N - 1) v += y1;
+        acc[m * sn] = v;
       }
     }
-    __syncthreads();
   }
-
+  __syncthreads();
   if (active) {
     double *Aue = A.Au + A.node_off[e];
 #pragma unroll
-    for (int m = 0; m < N3 / TPE; m++) Aue[lt + TPE * m] = ACC[lt + TPE * m];
+    for (int m = 0; m < N3 / TPE; m++) Aue[lt + TPE * m] = ACC[(lt % N) + SJ * (lt / N) + SK * m];
   }
 }
 
