@@ -158,10 +158,11 @@ int d4b_mesh_create(const d4b_mesh_desc_t *D, d4b_mesh_t **out)
     m->send_node_begin_h = (int64_t *)calloc(np + 1, sizeof(int64_t));
     m->recv_node_begin_h = (int64_t *)calloc(np + 1, sizeof(int64_t));
     int64_t sn = 0;
+    std::vector<int64_t> soff((size_t)D->send_begin[np] + 1);
     for (int p = 0; p < np; p++) {
       m->send_node_begin_h[p] = sn;
       for (int j = D->send_begin[p]; j < D->send_begin[p + 1]; j++) {
-        int e = D->send_elem[j]; sn += D->node_off[e + 1] - D->node_off[e];
+        int e = D->send_elem[j]; soff[j] = sn; sn += D->node_off[e + 1] - D->node_off[e];
       }
       m->recv_node_begin_h[p] = D->node_off[nl + D->recv_begin[p]] - D->node_off[nl];
     }
@@ -170,6 +171,7 @@ int d4b_mesh_create(const d4b_mesh_desc_t *D, d4b_mesh_t **out)
     m->send_nodes = sn;
     int64_t dummy = 0;
     if ((rc = upload(&m->send_elem, D->send_elem, (size_t)D->send_begin[np], &dummy)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
+    if ((rc = upload(&m->send_off, soff.data(), (size_t)D->send_begin[np], &dummy)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
     D4B_CUDA(cudaMalloc((void **)&m->send_buf, (sn ? sn : 1) * sizeof(double)));
   }
   if ((rc = d4b_fast_classify(m, D)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
@@ -182,7 +184,7 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   if (!m) return;
   cudaFree(m->deg); cudaFree(m->node_off); cudaFree(m->degq); cudaFree(m->quad_off); cudaFree(m->G);
   cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost);
-  cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->send_elem); cudaFree(m->send_buf);
+  cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
   for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); }
   cudaFree(m->generic_list);
   free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
@@ -205,8 +207,9 @@ int d4b_set_ghost_host(d4b_mesh_t *m, const double *ug)
 int d4b_apply_dev(d4b_mesh_t *m, const double *u, double *Au, void *stream)
 {
   cudaStream_t st = (cudaStream_t)stream;
-  int handled = 0;
-  int rc = d4b_launch_fast(m, u, Au, st, &handled);
+  int handled = 0, rc;
+  if (m->n_peers > 0 && d4b_comm_size() > 1 && (rc = d4b_halo_exchange(m, u, stream)) != D4B_OK) return rc;
+  rc = d4b_launch_fast(m, u, Au, st, &handled);
   if (rc != D4B_OK) return rc;
   return rc;
 }

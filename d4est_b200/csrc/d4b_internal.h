@@ -41,7 +41,7 @@ struct d4b_mesh {
   size_t generic_smem;
   /* halo lists */
   int n_peers; int32_t *peer_rank_h, *send_begin_h, *recv_begin_h; int32_t *send_elem;
-  int64_t *send_node_begin_h, *recv_node_begin_h; double *send_buf; int64_t send_nodes;
+  int64_t *send_node_begin_h, *recv_node_begin_h; double *send_buf; int64_t send_nodes; int64_t *send_off; /* device: offset of each send slot in send_buf */
   cudaStream_t stream;
   d4b_fast_bucket fast[D4B_MAX_BUCKETS]; int n_fast;
   int32_t *generic_list; int n_generic;   /* elements left to the generic kernel */

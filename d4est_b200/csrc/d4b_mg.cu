@@ -1,0 +1,305 @@
+/* d4b_mg.cu -- multigrid on cached device levels: element-local restriction / prolongation and the
+ * V-cycle driver.  The reference defines its hierarchy by MUTATING the live p4est every cycle
+ * (p4est_coarsen_ext / p4est_refine_ext, Solver/d4est_solver_multigrid.c:984,1199) and transfers in
+ * the callbacks (Solver/d4est_solver_multigrid_callbacks.h:109 restriction r_H = P^T r_h, :236
+ * prolongation e_h = P e_H, coarse degree = min over children :50-75).  Here the host walks that
+ * hierarchy ONCE, emits one transfer table per level pair, and every level stays resident. */
+#include "d4b_internal.h"
+#include "d4b_ops.h"
+#include <vector>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+
+/* 1-D prolongation pool: P[degH][degh][variant] (Nh x NH), variant 0 = same cell (p-prolong,
+ * dGMath/d4est_operators.c:995), 1/2 = lower/upper child (hp-prolong :944-993) */
+struct mg_pool { int off[D4B_NDEG][D4B_NDEG][3]; const double *pool; };
+__constant__ mg_pool c_mg;
+static bool g_mg_ready = false;
+
+static int mg_pool_init()
+{
+  if (g_mg_ready) return D4B_OK;
+  static mg_pool h;
+  std::vector<double> pool;
+  double buf[D4B_OPS_MAXN * D4B_OPS_MAXN];
+  for (int dH = 0; dH < D4B_NDEG; dH++)
+    for (int dh = 0; dh < D4B_NDEG; dh++)
+      for (int v = 0; v < 3; v++) {
+        h.off[dH][dh][v] = (int)pool.size();
+        if (dH < 1 || dh < dH) continue;
+        d4b_ops_prolong(dH, dh, v - 1, buf);
+        pool.insert(pool.end(), buf, buf + (dh + 1) * (dH + 1));
+      }
+  double *d = nullptr;
+  D4B_CUDA(cudaMalloc((void **)&d, pool.size() * sizeof(double)));
+  D4B_CUDA(cudaMemcpy(d, pool.data(), pool.size() * sizeof(double), cudaMemcpyHostToDevice));
+  h.pool = d;
+  D4B_CUDA(cudaMemcpyToSymbol(c_mg, &h, sizeof h));
+  g_mg_ready = true;
+  return D4B_OK;
+}
+
+struct d4b_mg_transfer {
+  int n_coarse;
+  int32_t *kind, *degH, *child_deg;     /* device: [nH], [nH], [8 nH] */
+  int64_t *coarse_off, *child_off;      /* device: [nH], [8 nH]       */
+  int max_n;
+};
+
+/* y(dims with axis ax -> rows) = M applied along ax; M(r,k) = M[r*rs + k*cs] */
+__device__ __forceinline__ void mg_contract(const double *__restrict__ M, int rs, int cs, int rows, int cols,
+                                            const double *in, double *out, int n0, int n1, int n2, int ax, bool acc)
+{
+  const int o0 = ax == 0 ? rows : n0, o1 = ax == 1 ? rows : n1, o2 = ax == 2 ? rows : n2;
+  const int total = o0 * o1 * o2, stride = ax == 0 ? 1 : (ax == 1 ? n0 : n0 * n1);
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    int i0 = idx % o0, i1 = (idx / o0) % o1, i2 = idx / (o0 * o1);
+    int r = ax == 0 ? i0 : (ax == 1 ? i1 : i2);
+    int base = (ax == 0 ? 0 : i0) + n0 * ((ax == 1 ? 0 : i1) + n1 * (ax == 2 ? 0 : i2));
+    double s = 0.;
+    for (int k = 0; k < cols; k++) s = fma(__ldg(&M[r * rs + k * cs]), in[base + k * stride], s);
+    out[idx] = acc ? out[idx] + s : s;
+  }
+  __syncthreads();
+}
+
+/* one CTA per coarse element.  dir = 0: restriction xH = sum_c P_c^T xh_c;  dir = 1: prolongation */
+__global__ void __launch_bounds__(128)
+k_mg_transfer(d4b_mg_transfer T, int dir, const double *__restrict__ src, double *__restrict__ dst, int NX)
+{
+  extern __shared__ double sm[];
+  const int e = blockIdx.x, NX3 = NX * NX * NX;
+  double *a = sm, *b = a + NX3, *c = b + NX3;
+  const int dH = T.degH[e], NH = dH + 1, NH3 = NH * NH * NH;
+  const int nchild = T.kind[e] == 1 ? 8 : 1;
+  if (dir == 0) for (int i = threadIdx.x; i < NH3; i += blockDim.x) c[i] = 0.;
+  else for (int i = threadIdx.x; i < NH3; i += blockDim.x) c[i] = src[T.coarse_off[e] + i];
+  __syncthreads();
+  for (int ch = 0; ch < nchild; ch++) {
+    const int dh = T.child_deg[8 * e + ch], Nh = dh + 1, Nh3 = Nh * Nh * Nh;
+    const int64_t fo = T.child_off[8 * e + ch];
+    const int vx = nchild == 8 ? 1 + (ch & 1) : 0, vy = nchild == 8 ? 1 + ((ch >> 1) & 1) : 0,
+              vz = nchild == 8 ? 1 + ((ch >> 2) & 1) : 0;
+    const double *Px = c_mg.pool + c_mg.off[dH][dh][vx], *Py = c_mg.pool + c_mg.off[dH][dh][vy],
+                 *Pz = c_mg.pool + c_mg.off[dH][dh][vz];
+    if (dir == 0) { /* restriction: transposes (Nh -> NH per axis), accumulate over children */
+      for (int i = threadIdx.x; i < Nh3; i += blockDim.x) a[i] = src[fo + i];
+      __syncthreads();
+      mg_contract(Px, 1, NH, NH, Nh, a, b, Nh, Nh, Nh, 0, false);
+      mg_contract(Py, 1, NH, NH, Nh, b, a, NH, Nh, Nh, 1, false);
+      mg_contract(Pz, 1, NH, NH, Nh, a, c, NH, NH, Nh, 2, true);
+    } else {        /* prolongation */
+      mg_contract(Px, NH, 1, Nh, NH, c, a, NH, NH, NH, 0, false);
+      mg_contract(Py, NH, 1, Nh, NH, a, b, Nh, NH, NH, 1, false);
+      mg_contract(Pz, NH, 1, Nh, NH, b, a, Nh, Nh, NH, 2, false);
+      for (int i = threadIdx.x; i < Nh3; i += blockDim.x) dst[fo + i] = a[i];
+      __syncthreads();
+    }
+  }
+  if (dir == 0) for (int i = threadIdx.x; i < NH3; i += blockDim.x) dst[T.coarse_off[e] + i] = c[i];
+}
+
+template <class T> static int up(T **dst, const T *src, size_t n)
+{
+  D4B_CUDA(cudaMalloc((void **)dst, (n ? n : 1) * sizeof(T)));
+  if (n) D4B_CUDA(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+  return D4B_OK;
+}
+
+struct d4b_mg {
+  int n_levels;
+  d4b_mesh **lvl;            /* 0 = coarsest ... n_levels-1 = finest */
+  d4b_mg_transfer **tr;      /* tr[l]: between level l (coarse) and l+1 (fine) */
+  d4b_mg_params_t par;
+  double *eigs;              /* per level spectral bound (cheby->eigs[level]) */
+  double *u, *rhs, *r;       /* per-level stacked work vectors for levels < finest */
+  int64_t *off;              /* offset of level l inside the stacks */
+  double *work;              /* 3 * max nodes */
+  int vcycles_done;
+};
+
+extern "C" {
+
+int d4b_mg_transfer_create(int n_coarse, const int32_t *kind, const int32_t *degH, const int64_t *coarse_off,
+                           const int32_t *child_deg, const int64_t *child_off, d4b_mg_transfer_t **out)
+{
+  int rc = mg_pool_init(); if (rc) return rc;
+  d4b_mg_transfer *T = (d4b_mg_transfer *)calloc(1, sizeof *T);
+  T->n_coarse = n_coarse;
+  for (int e = 0; e < n_coarse; e++) {
+    int nc = kind[e] == 1 ? 8 : 1;
+    if (degH[e] < 1 || degH[e] > D4B_MAX_DEG) { d4b_set_error("mg: degH out of range"); free(T); return D4B_EINVAL; }
+    if (degH[e] + 1 > T->max_n) T->max_n = degH[e] + 1;
+    for (int c = 0; c < nc; c++) {
+      int dh = child_deg[8 * e + c];
+      if (dh < degH[e] || dh > D4B_MAX_DEG) { d4b_set_error("mg: child degree below coarse degree"); free(T); return D4B_EINVAL; }
+      if (dh + 1 > T->max_n) T->max_n = dh + 1;
+    }
+  }
+  if ((rc = up(&T->kind, kind, n_coarse)) || (rc = up(&T->degH, degH, n_coarse)) ||
+      (rc = up(&T->coarse_off, coarse_off, n_coarse)) || (rc = up(&T->child_deg, child_deg, 8 * (size_t)n_coarse)) ||
+      (rc = up(&T->child_off, child_off, 8 * (size_t)n_coarse))) return rc;
+  *out = T;
+  return D4B_OK;
+}
+void d4b_mg_transfer_destroy(d4b_mg_transfer_t *T)
+{
+  if (!T) return;
+  cudaFree(T->kind); cudaFree(T->degH); cudaFree(T->coarse_off); cudaFree(T->child_deg); cudaFree(T->child_off); free(T);
+}
+static int transfer(d4b_mg_transfer *T, int dir, const double *src, double *dst, cudaStream_t st)
+{
+  if (T->n_coarse == 0) return D4B_OK;
+  size_t smem = 3 * (size_t)T->max_n * T->max_n * T->max_n * sizeof(double);
+  static size_t attr = 0;
+  if (smem > 48 * 1024 && smem > attr) {
+    D4B_CUDA(cudaFuncSetAttribute(k_mg_transfer, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = smem;
+  }
+  k_mg_transfer<<<T->n_coarse, 128, smem, st>>>(*T, dir, src, dst, T->max_n);
+  D4B_CUDA(cudaGetLastError()); d4b_count_launch(1);
+  return D4B_OK;
+}
+/* r_H = P^T r_h  (multigrid_callbacks.h:109-175) */
+int d4b_mg_restrict(d4b_mg_transfer_t *T, const double *fine, double *coarse, void *stream)
+{ return transfer(T, 0, fine, coarse, (cudaStream_t)stream); }
+/* e_h = P e_H    (multigrid_callbacks.h:236-300) */
+int d4b_mg_prolong(d4b_mg_transfer_t *T, const double *coarse, double *fine, void *stream)
+{ return transfer(T, 1, coarse, fine, (cudaStream_t)stream); }
+
+int d4b_mg_create(int n_levels, d4b_mesh_t **levels, d4b_mg_transfer_t **transfers, const d4b_mg_params_t *par,
+                  d4b_mg_t **out)
+{
+  if (n_levels < 2) { d4b_set_error("multigrid needs >= 2 levels (multigrid.c:1434)"); return D4B_EINVAL; }
+  d4b_mg *g = (d4b_mg *)calloc(1, sizeof *g);
+  g->n_levels = n_levels; g->par = *par;
+  g->lvl = (d4b_mesh **)malloc(n_levels * sizeof(void *)); g->tr = (d4b_mg_transfer **)malloc(n_levels * sizeof(void *));
+  g->off = (int64_t *)calloc(n_levels + 1, sizeof(int64_t)); g->eigs = (double *)calloc(n_levels, sizeof(double));
+  int64_t tot = 0, mx = 0;
+  for (int l = 0; l < n_levels; l++) {
+    g->lvl[l] = levels[l]; g->tr[l] = l < n_levels - 1 ? transfers[l] : nullptr;
+    g->off[l] = tot; if (l < n_levels - 1) tot += levels[l]->local_nodes;
+    if (levels[l]->local_nodes > mx) mx = levels[l]->local_nodes;
+  }
+  size_t nb = (size_t)(tot ? tot : 1) * sizeof(double);
+  D4B_CUDA(cudaMalloc((void **)&g->u, nb)); D4B_CUDA(cudaMalloc((void **)&g->rhs, nb));
+  D4B_CUDA(cudaMalloc((void **)&g->r, nb + levels[n_levels - 1]->local_nodes * sizeof(double)));
+  D4B_CUDA(cudaMalloc((void **)&g->work, 3 * (size_t)mx * sizeof(double)));
+  *out = g;
+  return D4B_OK;
+}
+void d4b_mg_destroy(d4b_mg_t *g)
+{
+  if (!g) return;
+  cudaFree(g->u); cudaFree(g->rhs); cudaFree(g->r); cudaFree(g->work);
+  free(g->lvl); free(g->tr); free(g->off); free(g->eigs); free(g);
+}
+int d4b_mg_get_eigs(d4b_mg_t *g, double *eigs) { memcpy(eigs, g->eigs, g->n_levels * sizeof(double)); return D4B_OK; }
+
+} /* extern C */
+
+/* smoother = [cg_eigs] + Chebyshev (smoother_cheby.c:264-360); `down` selects the reuse policy of
+ * d4est_solver_multigrid_smoother_cheby_update (:221-262) */
+static int mg_smooth(d4b_mg *g, int l, double *u, const double *rhs, double *r, int down, void *stream)
+{
+  const d4b_mg_params_t &p = g->par;
+  int compute = down ? !(p.eigs_reuse_fromlastvcycle && g->vcycles_done != 0)
+                     : !(p.eigs_reuse_fromdownvcycle || (p.eigs_reuse_fromlastvcycle && g->vcycles_done != 0));
+  int rc;
+  if (compute) {
+    if ((rc = d4b_cg_eigs(g->lvl[l], u, rhs, p.cheby_eigs_cg_imax, p.use_new_cg_eigs, &g->eigs[l], g->work, stream))) return rc;
+    g->eigs[l] *= p.cheby_eigs_max_multiplier;
+  }
+  return d4b_cheby_iterate(g->lvl[l], u, rhs, r, p.cheby_imax, g->eigs[l] / p.cheby_eigs_lmax_lmin_ratio, g->eigs[l], 1,
+                           g->work, stream);
+}
+
+extern "C" {
+
+/* One V-cycle on the cached levels: restates d4est_solver_multigrid_vcycle
+ * (Solver/d4est_solver_multigrid.c:751-1330).  u, rhs: finest-level device vectors. */
+int d4b_mg_vcycle(d4b_mg_t *g, double *u, const double *rhs, double *r2_local, void *stream)
+{
+  const int top = g->n_levels - 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  double *rtop = g->r + g->off[top]; /* finest-level residual lives after the coarse stack */
+  /* down sweep (:847-1110) */
+  for (int l = top; l > 0; --l) {
+    double *ul = l == top ? u : g->u + g->off[l];
+    const double *fl = l == top ? rhs : g->rhs + g->off[l];
+    double *rl = l == top ? rtop : g->r + g->off[l];
+    if (l != top) D4B_CUDA(cudaMemsetAsync(ul, 0, g->lvl[l]->local_nodes * sizeof(double), st));
+    if ((rc = mg_smooth(g, l, ul, fl, rl, 1, stream))) return rc;
+    if ((rc = d4b_mg_restrict(g->tr[l - 1], rl, g->rhs + g->off[l - 1], stream))) return rc;
+  }
+  /* bottom solve (:1112-1160) */
+  {
+    d4b_mesh *m0 = g->lvl[0];
+    double *u0 = g->u + g->off[0], *f0 = g->rhs + g->off[0], *r0 = g->r + g->off[0];
+    const d4b_mg_params_t &p = g->par;
+    D4B_CUDA(cudaMemsetAsync(u0, 0, m0->local_nodes * sizeof(double), st));
+    if (p.bottom_kind == 1) { /* mg_bottom_solver_cg (bottom_solver_cg.c:59-190) */
+      if ((rc = d4b_cg_solve(m0, u0, f0, p.bottom_imax, p.bottom_atol, p.bottom_rtol, nullptr, nullptr, g->work, stream))) return rc;
+    } else {                  /* mg_bottom_solver_cheby (bottom_solver_cheby.c:59-113) */
+      double eig = 0.;
+      if ((rc = d4b_cg_eigs(m0, u0, f0, p.bottom_eigs_cg_imax, p.use_new_cg_eigs, &eig, g->work, stream))) return rc;
+      eig *= p.bottom_eigs_max_multiplier; g->eigs[0] = eig;
+      if ((rc = d4b_cheby_iterate(m0, u0, f0, r0, p.bottom_imax, eig / p.bottom_eigs_lmax_lmin_ratio, eig, 1, g->work, stream))) return rc;
+    }
+  }
+  /* up sweep (:1168-1300): prolong the correction, add, post-smooth */
+  for (int l = 0; l < top; ++l) {
+    double *uf = (l + 1 == top) ? u : g->u + g->off[l + 1];
+    const double *ff = (l + 1 == top) ? rhs : g->rhs + g->off[l + 1];
+    double *rf = (l + 1 == top) ? rtop : g->r + g->off[l + 1];
+    if ((rc = d4b_mg_prolong(g->tr[l], g->u + g->off[l], rf, stream))) return rc;
+    if ((rc = d4b_vec_axpy(g->lvl[l + 1]->local_nodes, 1.0, rf, uf, stream))) return rc;
+    if ((rc = mg_smooth(g, l + 1, uf, ff, rf, 0, stream))) return rc;
+  }
+  if (r2_local) return d4b_vec_dot(g->lvl[top]->local_nodes, rtop, rtop, r2_local, stream);
+  return D4B_OK;
+}
+
+/* V-cycles until the residual criterion: restates d4est_solver_multigrid_solve (:1420-1500) */
+int d4b_mg_solve(d4b_mg_t *g, double *u, const double *rhs, int *vcycles, double *r2_final, void *stream)
+{
+  const int top = g->n_levels - 1; const int64_t n = g->lvl[top]->local_nodes;
+  double *Au = g->work, *r = g->work + n, r2, r2_last;
+  int rc;
+  if ((rc = d4b_apply_dev(g->lvl[top], u, Au, stream))) return rc;
+  if ((rc = d4b_vec_axpyeqz(n, -1., Au, rhs, r, stream))) return rc;
+  if ((rc = d4b_vec_dot(n, r, r, &r2, stream))) return rc;
+  r2_last = r2; g->vcycles_done = 0;
+  const double stoptol = g->par.vcycle_rtol * g->par.vcycle_rtol * r2 + g->par.vcycle_atol * g->par.vcycle_atol;
+  while (g->vcycles_done < g->par.vcycle_imax && r2 > stoptol) {
+    if ((rc = d4b_mg_vcycle(g, u, rhs, nullptr, stream))) return rc;
+    if ((rc = d4b_apply_dev(g->lvl[top], u, Au, stream))) return rc;
+    if ((rc = d4b_vec_axpyeqz(n, -1., Au, rhs, r, stream))) return rc;
+    if ((rc = d4b_vec_dot(n, r, r, &r2, stream))) return rc;
+    g->vcycles_done++;
+    if (sqrt(r2 / r2_last) >= .99) break;
+    r2_last = r2;
+  }
+  if (vcycles) *vcycles = g->vcycles_done;
+  if (r2_final) *r2_final = r2;
+  return D4B_OK;
+}
+
+/* preconditioner apply z = MG(r) from a zero guess: restates d4est_krylov_pc_multigrid_apply
+ * (Solver/d4est_krylov_pc_multigrid.c:41-75); signature = d4b_pc_fcn_t with ctx = d4b_mg_t* */
+int d4b_mg_pc_apply(void *ctx, const double *r_dev, double *z_dev, void *stream)
+{
+  d4b_mg *g = (d4b_mg *)ctx;
+  D4B_CUDA(cudaMemsetAsync(z_dev, 0, g->lvl[g->n_levels - 1]->local_nodes * sizeof(double), (cudaStream_t)stream));
+  return d4b_mg_solve(g, z_dev, r_dev, nullptr, nullptr, stream);
+}
+
+/* MG-preconditioned flexible CG in one call (BASELINE config 4) */
+int d4b_mg_fcg_solve(d4b_mg_t *g, double *u, const double *rhs, int imax, double atol, double rtol, int *iters,
+                     double *final_res, double *work_6n, void *stream)
+{
+  return d4b_fcg_solve(g->lvl[g->n_levels - 1], u, rhs, imax, atol, rtol, d4b_mg_pc_apply, g, iters, final_res, work_6n, stream);
+}
+
+} /* extern C */

@@ -136,6 +136,17 @@ int d4b_apply_dev(d4b_mesh_t *m, const double *u_dev, double *Au_dev, void *cuda
 int d4b_set_ghost_host(d4b_mesh_t *m, const double *ughost_host);
 int64_t d4b_kernel_launches(void);   /* number of d4b kernels launched so far          */
 
+/* ---- rank boundary (one p4est rank = one GPU): replaces d4est_ghost_data_exchange
+ *      (Mesh/d4est_ghost_data.c:143-255) and sc_allreduce (Solver/d4est_solver_cg.c:139,165) by
+ *      ncclSend/ncclRecv + ncclAllReduce.  The 128-byte id is created on rank 0
+ *      (d4b_comm_unique_id) and broadcast by the host program (MPI_Bcast in d4est).  With a
+ *      communicator, d4b_apply_dev exchanges the halo of u before the element kernels.        */
+int d4b_comm_unique_id(char *out128);
+int d4b_comm_init(int rank, int nranks, const char *id128);
+int d4b_comm_finalize(void);
+int d4b_comm_size(void);
+int d4b_halo_exchange(d4b_mesh_t *m, const double *u_dev, void *cuda_stream);
+
 /* ---- device vectors / BLAS-1 (LinearAlgebra/d4est_linalg.c:179-235) -------------- */
 int d4b_dev_alloc(size_t bytes, void **dptr);
 int d4b_dev_free(void *dptr);
@@ -144,6 +155,60 @@ int d4b_d2h(void *dst_host, const void *src_dev, size_t bytes, void *cuda_stream
 int d4b_sync(void *cuda_stream);
 int d4b_host_alloc_pinned(size_t bytes, void **hptr);
 int d4b_host_free_pinned(void *hptr);
+int d4b_vec_axpy(int64_t n, double a, const double *x, double *y, void *cuda_stream);      /* y += a x      */
+int d4b_vec_xpby(int64_t n, const double *x, double b, double *y, void *cuda_stream);      /* y = x + b y   */
+int d4b_vec_axpyeqz(int64_t n, double a, const double *x, const double *y, double *z, void *cuda_stream);
+int d4b_vec_scale(int64_t n, double a, double *x, void *cuda_stream);
+int d4b_vec_copy(int64_t n, const double *x, double *y, void *cuda_stream);
+int d4b_vec_zero(int64_t n, double *x, void *cuda_stream);
+int d4b_vec_dot(int64_t n, const double *x, const double *y, double *result_host, void *cuda_stream);
+
+/* ---- Chebyshev smoother + CG spectral bound (device vectors; `work` = caller scratch)
+ *      d4est_solver_multigrid_smoother_cheby_iterate_aux  Solver/d4est_solver_multigrid_smoother_cheby.c:81
+ *      cg_eigs                                            Solver/d4est_solver_cg_eigs.c:115            */
+int d4b_cheby_iterate(d4b_mesh_t *m, double *u, const double *rhs, double *r, int iter, double lmin,
+                      double lmax, int residual_at_end, double *work_2n, void *cuda_stream);
+int d4b_cg_eigs(d4b_mesh_t *m, double *u, const double *rhs, int imax, int use_new, double *spectral_bound,
+                double *work_3n, void *cuda_stream);
+/* ---- Krylov drivers: d4est_solver_cg_solve Solver/d4est_solver_cg.c:76,
+ *      d4est_solver_fcg_solve Solver/d4est_solver_fcg_improved.c:97 (pc = d4est_krylov_pc_t.pc_apply) */
+typedef int (*d4b_pc_fcn_t)(void *ctx, const double *r_dev, double *z_dev, void *cuda_stream);
+int d4b_cg_solve(d4b_mesh_t *m, double *u, const double *rhs, int imax, double atol, double rtol,
+                 int *iters, double *res2, double *work_3n, void *cuda_stream);
+int d4b_fcg_solve(d4b_mesh_t *m, double *u, const double *rhs, int imax, double atol, double rtol,
+                  d4b_pc_fcn_t pc, void *pc_ctx, int *iters, double *final_res, double *work_6n,
+                  void *cuda_stream);
+
+/* ---- multigrid on cached levels.  Transfer table between two levels (one entry per COARSE
+ *      element; d4est_solver_multigrid_refine_data_t{hrefine,degh[8],degH} Solver/d4est_solver_multigrid.h:12-18):
+ *      kind 0 = same cell (p-prolongation, 1 child), kind 1 = 8 children (hp-prolongation, child c =
+ *      bits (r,s,t)); offsets are into the coarse / fine nodal vectors.                              */
+typedef struct d4b_mg_transfer d4b_mg_transfer_t;
+typedef struct d4b_mg d4b_mg_t;
+typedef struct d4b_mg_params {  /* [multigrid], [mg_smoother_cheby], [mg_bottom_solver_*] input keys */
+  int32_t vcycle_imax; double vcycle_rtol, vcycle_atol;
+  int32_t cheby_imax, cheby_eigs_cg_imax; double cheby_eigs_lmax_lmin_ratio, cheby_eigs_max_multiplier;
+  int32_t eigs_reuse_fromdownvcycle, eigs_reuse_fromlastvcycle, use_new_cg_eigs;
+  int32_t bottom_kind;          /* 0 = mg_bottom_solver_cheby, 1 = mg_bottom_solver_cg */
+  int32_t bottom_imax, bottom_eigs_cg_imax; double bottom_eigs_lmax_lmin_ratio, bottom_eigs_max_multiplier;
+  double bottom_atol, bottom_rtol;
+} d4b_mg_params_t;
+int d4b_mg_transfer_create(int n_coarse, const int32_t *kind, const int32_t *degH, const int64_t *coarse_off,
+                           const int32_t *child_deg /*[8 n]*/, const int64_t *child_off /*[8 n]*/,
+                           d4b_mg_transfer_t **out);
+void d4b_mg_transfer_destroy(d4b_mg_transfer_t *T);
+int d4b_mg_restrict(d4b_mg_transfer_t *T, const double *fine_dev, double *coarse_dev, void *cuda_stream);
+int d4b_mg_prolong(d4b_mg_transfer_t *T, const double *coarse_dev, double *fine_dev, void *cuda_stream);
+/* levels[0] = coarsest ... levels[n-1] = finest; transfers[l] joins l (coarse) and l+1 (fine) */
+int d4b_mg_create(int n_levels, d4b_mesh_t **levels, d4b_mg_transfer_t **transfers, const d4b_mg_params_t *par,
+                  d4b_mg_t **out);
+void d4b_mg_destroy(d4b_mg_t *g);
+int d4b_mg_get_eigs(d4b_mg_t *g, double *eigs_per_level);
+int d4b_mg_vcycle(d4b_mg_t *g, double *u_dev, const double *rhs_dev, double *r2_local, void *cuda_stream);
+int d4b_mg_solve(d4b_mg_t *g, double *u_dev, const double *rhs_dev, int *vcycles, double *r2_final, void *cuda_stream);
+int d4b_mg_pc_apply(void *mg, const double *r_dev, double *z_dev, void *cuda_stream);
+int d4b_mg_fcg_solve(d4b_mg_t *g, double *u_dev, const double *rhs_dev, int imax, double atol, double rtol,
+                     int *iters, double *final_res, double *work_6n, void *cuda_stream);
 
 #ifdef __cplusplus
 }

@@ -25,12 +25,19 @@
 #include <d4est_util.h>
 #include <time.h>
 #include <math.h>
+#include <d4est_solver_cg_eigs.h>
+#include <d4est_solver_multigrid_smoother_cheby.h>
 #include "d4est_b200_glue.h"
 #include "fixture_io.h"
 
 static double poly_fcn(double x, double y, double z, void *user) { (void)user; return x * x + y * y + z * z; }
 static double sin_fcn(double x, double y, double z, void *user)
 { (void)user; return sin(M_PI * x) * sin(M_PI * y) * sin(M_PI * z); }
+
+static void ref_apply_lhs(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost_data_t *gd, d4est_elliptic_data_t *v,
+                          d4est_operators_t *ops, d4est_geometry_t *geom, d4est_quadrature_t *quad,
+                          d4est_mesh_data_t *factors, void *user)
+{ d4est_laplacian_with_opt_apply_aij(p4est, ghost, gd, v, (d4est_laplacian_with_opt_flux_data_t *)user, ops, geom, quad, factors, 0); }
 
 static double now_s(void)
 { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec + 1e-9 * t.tv_nsec; }
@@ -129,6 +136,22 @@ int main(int argc, char **argv)
     fix_write(f, "u", FIX_F64, n, u);
     fix_write(f, "Au_ref_baseline", FIX_F64, n, Au0);
     fix_write(f, "Au_ref_with_opt", FIX_F64, n, Au1);
+    { /* reference smoother pieces on the same operator: cg_eigs (Solver/d4est_solver_cg_eigs.c:115) from a
+         zero guess with rhs = A u, then d4est_solver_multigrid_smoother_cheby_iterate_aux (:81) */
+      double *su = P4EST_ALLOC_ZERO(double, n), *sAu = P4EST_ALLOC_ZERO(double, n), *sr = P4EST_ALLOC_ZERO(double, n);
+      d4est_elliptic_eqns_t fc; fc.apply_lhs = ref_apply_lhs; fc.build_residual = NULL; fc.user = fl1;
+      d4est_elliptic_data_t sv; memset(&sv, 0, sizeof sv);
+      sv.u = su; sv.Au = sAu; sv.rhs = Au1; sv.local_nodes = n; sv.field_types = &ft; sv.num_of_fields = 1;
+      double eig = -1.;
+      cg_eigs(p4est, &sv, &fc, ghost, gd, ops, geom, quad, factors, 10, 0, 0, &eig);
+      fix_write(f, "sol_eig", FIX_F64, 1, &eig);
+      fix_write(f, "sol_u_after_eigs", FIX_F64, n, su);
+      d4est_solver_multigrid_smoother_cheby_iterate_aux(p4est, ops, geom, quad, factors, ghost, gd, &sv, &fc, sr, 8,
+                                                        eig / 30., eig, 0, 0, 1);
+      fix_write(f, "sol_u_after_cheby", FIX_F64, n, su);
+      fix_write(f, "sol_r_after_cheby", FIX_F64, n, sr);
+      P4EST_FREE(su); P4EST_FREE(sAu); P4EST_FREE(sr);
+    }
     fclose(f);
     d4est_b200_flatten_free(D);
   }

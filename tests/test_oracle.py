@@ -53,3 +53,19 @@ def test_operator_symmetry_homogeneous(golden_dir):
     x, y = rng.standard_normal(fx["u"].size), rng.standard_normal(fx["u"].size)
     a, b = y @ dg_oracle.apply(fx, x), x @ dg_oracle.apply(fx, y)
     assert abs(a - b) < 1e-11 * max(abs(a), 1.0)
+
+
+@pytest.mark.parametrize("name", ["brick_p3_l2", "cubed_sphere_hp1"])
+def test_solver_oracle_matches_reference_cg_eigs_and_cheby(golden_dir, name):
+    """cg_eigs (Solver/d4est_solver_cg_eigs.c:115) and the Chebyshev iteration
+    (Solver/d4est_solver_multigrid_smoother_cheby.c:81) run by the UNMODIFIED reference in the harness."""
+    import solver_oracle as so
+    fx = fixture.load(os.path.join(golden_dir, name + ".fix"))
+    A = lambda v: dg_oracle.apply(fx, v)
+    rhs = fx["Au_ref_with_opt"]
+    eig, u1 = so.cg_eigs(A, np.zeros_like(rhs), rhs, 10)
+    assert abs(eig - fx["sol_eig"][0]) < 1e-10 * abs(eig)
+    assert rel(u1, fx["sol_u_after_eigs"]) < 1e-10
+    u2, r2 = so.cheby_iterate(A, fx["sol_u_after_eigs"].copy(), rhs, 8, fx["sol_eig"][0] / 30., fx["sol_eig"][0])
+    assert rel(u2, fx["sol_u_after_cheby"]) < 1e-11
+    assert rel(r2, fx["sol_r_after_cheby"]) < 1e-10
