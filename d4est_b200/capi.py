@@ -65,7 +65,97 @@ SYMBOLS = {
     "d4b_sync": (C.c_int, [_P]),
     "d4b_host_alloc_pinned": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
     "d4b_host_free_pinned": (C.c_int, [_P]),
+    "d4b_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "d4b_comm_init": (C.c_int, [C.c_int, C.c_int, C.c_char_p]),
+    "d4b_comm_finalize": (C.c_int, []),
+    "d4b_comm_size": (C.c_int, []),
+    "d4b_halo_exchange": (C.c_int, [_P, _P, _P]),
+    "d4b_vec_axpy": (C.c_int, [C.c_int64, C.c_double, _P, _P, _P]),
+    "d4b_vec_xpby": (C.c_int, [C.c_int64, _P, C.c_double, _P, _P]),
+    "d4b_vec_axpyeqz": (C.c_int, [C.c_int64, C.c_double, _P, _P, _P, _P]),
+    "d4b_vec_scale": (C.c_int, [C.c_int64, C.c_double, _P, _P]),
+    "d4b_vec_copy": (C.c_int, [C.c_int64, _P, _P, _P]),
+    "d4b_vec_zero": (C.c_int, [C.c_int64, _P, _P]),
+    "d4b_vec_dot": (C.c_int, [C.c_int64, _P, _P, C.POINTER(C.c_double), _P]),
+    "d4b_cheby_iterate": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_double, C.c_double, C.c_int, _P, _P]),
+    "d4b_cg_eigs": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.POINTER(C.c_double), _P, _P]),
+    "d4b_cg_solve": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_double), _P, _P]),
+    "d4b_fcg_solve": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, _P, _P, C.POINTER(C.c_int), C.POINTER(C.c_double), _P, _P]),
+    "d4b_mg_transfer_create": (C.c_int, [C.c_int, _P, _P, _P, _P, _P, C.POINTER(_P)]),
+    "d4b_mg_transfer_destroy": (None, [_P]),
+    "d4b_mg_restrict": (C.c_int, [_P, _P, _P, _P]),
+    "d4b_mg_prolong": (C.c_int, [_P, _P, _P, _P]),
+    "d4b_mg_create": (C.c_int, [C.c_int, C.POINTER(_P), C.POINTER(_P), _P, C.POINTER(_P)]),
+    "d4b_mg_destroy": (None, [_P]),
+    "d4b_mg_get_eigs": (C.c_int, [_P, _P]),
+    "d4b_mg_vcycle": (C.c_int, [_P, _P, _P, C.POINTER(C.c_double), _P]),
+    "d4b_mg_solve": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int), C.POINTER(C.c_double), _P]),
+    "d4b_mg_pc_apply": (C.c_int, [_P, _P, _P, _P]),
+    "d4b_mg_fcg_solve": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_double), _P, _P]),
 }
+
+
+class MGParams(C.Structure):  # d4b_mg_params_t
+    _fields_ = [("vcycle_imax", C.c_int32), ("vcycle_rtol", C.c_double), ("vcycle_atol", C.c_double),
+                ("cheby_imax", C.c_int32), ("cheby_eigs_cg_imax", C.c_int32),
+                ("cheby_eigs_lmax_lmin_ratio", C.c_double), ("cheby_eigs_max_multiplier", C.c_double),
+                ("eigs_reuse_fromdownvcycle", C.c_int32), ("eigs_reuse_fromlastvcycle", C.c_int32),
+                ("use_new_cg_eigs", C.c_int32), ("bottom_kind", C.c_int32), ("bottom_imax", C.c_int32),
+                ("bottom_eigs_cg_imax", C.c_int32), ("bottom_eigs_lmax_lmin_ratio", C.c_double),
+                ("bottom_eigs_max_multiplier", C.c_double), ("bottom_atol", C.c_double), ("bottom_rtol", C.c_double)]
+
+
+class DevVec:
+    """n doubles in HBM (d4b_dev_alloc); host copies only through .set / .get."""
+
+    def __init__(self, n, init=None):
+        self.n = int(n); self.ptr = _P()
+        check(lib().d4b_dev_alloc(self.n * 8, C.byref(self.ptr)))
+        if init is not None:
+            self.set(init)
+        else:
+            check(lib().d4b_vec_zero(self.n, self.ptr, None))
+
+    def set(self, a):
+        a = np.ascontiguousarray(a, np.float64); assert a.size <= self.n
+        check(lib().d4b_h2d(self.ptr, _ptr(a), a.size * 8, None)); check(lib().d4b_sync(None))
+
+    def get(self, n=None):
+        out = np.empty(self.n if n is None else n)
+        check(lib().d4b_d2h(out.ctypes.data_as(_P), self.ptr, out.size * 8, None)); check(lib().d4b_sync(None))
+        return out
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                lib().d4b_dev_free(self.ptr)
+        except Exception:
+            pass
+
+
+class Transfer:
+    def __init__(self, tab):
+        self._k = [np.ascontiguousarray(tab[k], dt) for k, dt in (("kind", np.int32), ("degH", np.int32),
+                   ("coarse_off", np.int64), ("child_deg", np.int32), ("child_off", np.int64))]
+        self.handle = _P()
+        check(lib().d4b_mg_transfer_create(len(self._k[0]), *[_ptr(a) for a in self._k], C.byref(self.handle)))
+
+
+class Multigrid:
+    """levels: list of MeshLevel, coarsest first; transfers[l] joins level l and l+1."""
+
+    def __init__(self, levels, transfers, **kw):
+        p = MGParams(vcycle_imax=1, vcycle_rtol=1e-15, vcycle_atol=0., cheby_imax=15, cheby_eigs_cg_imax=15,
+                     cheby_eigs_lmax_lmin_ratio=30., cheby_eigs_max_multiplier=1.1, eigs_reuse_fromdownvcycle=1,
+                     eigs_reuse_fromlastvcycle=0, use_new_cg_eigs=0, bottom_kind=0, bottom_imax=15,
+                     bottom_eigs_cg_imax=15, bottom_eigs_lmax_lmin_ratio=30., bottom_eigs_max_multiplier=1.1,
+                     bottom_atol=1e-15, bottom_rtol=1e-15)
+        for k, v in kw.items():
+            setattr(p, k, v)
+        self.params, self.levels, self.transfers = p, levels, transfers
+        L = (_P * len(levels))(*[l.handle for l in levels]); T = (_P * max(1, len(transfers)))(*[t.handle for t in transfers])
+        self.handle = _P()
+        check(lib().d4b_mg_create(len(levels), L, T, C.byref(p), C.byref(self.handle)))
 
 _lib = None
 
