@@ -1,0 +1,104 @@
+"""Device solver pieces (through the C ABI) against the reference's own cg_eigs / Chebyshev output
+(fixtures) and against the numpy restatements in oracle/solver_oracle.py."""
+import ctypes as C
+import os
+import numpy as np
+import pytest
+import d4est_b200
+from d4est_b200 import capi
+from d4est_b200.capi import DevVec, lib, check
+import fixture
+import dg_oracle
+import solver_oracle as so
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+
+@pytest.mark.parametrize("name", ["brick_p3_l2", "cubed_sphere_hp1"])
+def test_cg_eigs_and_cheby_match_reference(golden_dir, name):
+    fx = fixture.load(os.path.join(golden_dir, name + ".fix"))
+    lvl = d4est_b200.MeshLevel(fx); n = lvl.local_nodes
+    rhs, u, r, work = DevVec(n, fx["Au_ref_with_opt"]), DevVec(n), DevVec(n), DevVec(3 * n)
+    eig = C.c_double(0.)
+    check(lib().d4b_cg_eigs(lvl.handle, u.ptr, rhs.ptr, 10, 0, C.byref(eig), work.ptr, None))
+    assert abs(eig.value - fx["sol_eig"][0]) < 1e-9 * abs(eig.value)
+    assert rel(u.get(), fx["sol_u_after_eigs"]) < 1e-9
+    u.set(fx["sol_u_after_eigs"])
+    e = float(fx["sol_eig"][0])
+    check(lib().d4b_cheby_iterate(lvl.handle, u.ptr, rhs.ptr, r.ptr, 8, e / 30., e, 1, work.ptr, None))
+    assert rel(u.get(), fx["sol_u_after_cheby"]) < 1e-11
+    assert rel(r.get(), fx["sol_r_after_cheby"]) < 1e-10
+
+
+def test_vector_ops():
+    n = 100003
+    rng = np.random.default_rng(0); x, y = rng.standard_normal(n), rng.standard_normal(n)
+    X, Y, Z = DevVec(n, x), DevVec(n, y), DevVec(n)
+    d = C.c_double()
+    check(lib().d4b_vec_dot(n, X.ptr, Y.ptr, C.byref(d), None)); assert abs(d.value - x @ y) < 1e-9
+    check(lib().d4b_vec_axpy(n, 0.5, X.ptr, Y.ptr, None)); y = y + 0.5 * x; assert np.allclose(Y.get(), y, rtol=0, atol=1e-15)
+    check(lib().d4b_vec_xpby(n, X.ptr, -2.0, Y.ptr, None)); y = x - 2 * y; assert np.allclose(Y.get(), y, rtol=0, atol=1e-14)
+    check(lib().d4b_vec_axpyeqz(n, 3.0, X.ptr, Y.ptr, Z.ptr, None)); assert np.allclose(Z.get(), 3 * x + y, rtol=0, atol=1e-14)
+    check(lib().d4b_vec_scale(n, 0.25, Z.ptr, None)); assert np.allclose(Z.get(), 0.25 * (3 * x + y), rtol=0, atol=1e-14)
+
+
+def test_cg_and_fcg_match_oracle_iteration_counts(golden_dir):
+    fx = fixture.load(os.path.join(golden_dir, "brick_p3_l2.fix"))  # homogeneous data: linear SPD operator
+    lvl = d4est_b200.MeshLevel(fx); n = lvl.local_nodes
+    A = lambda v: dg_oracle.apply(fx, v)
+    rhs = np.random.default_rng(5).standard_normal(n)
+    uo, io, _ = so.cg_solve(A, np.zeros(n), rhs, 400, 0., 1e-10)
+    U, R, W = DevVec(n), DevVec(n, rhs), DevVec(6 * n)
+    it, r2 = C.c_int(), C.c_double()
+    check(lib().d4b_cg_solve(lvl.handle, U.ptr, R.ptr, 400, 0., 1e-10, C.byref(it), C.byref(r2), W.ptr, None))
+    assert abs(it.value - io) <= 1 and rel(U.get(), uo) < 1e-7
+    uf, kf = so.fcg_solve(A, np.zeros(n), rhs, 400, 0., 1e-10)
+    U2 = DevVec(n); res = C.c_double()
+    check(lib().d4b_fcg_solve(lvl.handle, U2.ptr, R.ptr, 400, 0., 1e-10, None, None, C.byref(it), C.byref(res), W.ptr, None))
+    assert abs(it.value - kf) <= 1 and rel(U2.get(), uf) < 1e-7
+
+
+def test_transfer_matches_oracle_and_is_adjoint():
+    deg = 2
+    tab = so.brick_transfer_table(2, deg)  # 4^3 -> 2^3 elements
+    # mixed degrees: children of coarse element 3 have degree 3 (p- and h-coarsening at once)
+    N3 = (deg + 1) ** 3
+    cd = tab["child_deg"].copy(); cd[24:32] = 3
+    sizes = (cd + 1) ** 3
+    tab["child_deg"] = cd; tab["child_off"] = np.concatenate([[0], np.cumsum(sizes)[:-1]]).astype(np.int64)
+    nf, nc = int(sizes.sum()), 8 * N3
+    T = capi.Transfer(tab)
+    rng = np.random.default_rng(2); xf, xc = rng.standard_normal(nf), rng.standard_normal(nc)
+    F, Cc = DevVec(nf, xf), DevVec(nc)
+    check(lib().d4b_mg_restrict(T.handle, F.ptr, Cc.ptr, None))
+    assert rel(Cc.get(), so.transfer(tab, xf, nc, True)) < 1e-13
+    Cc.set(xc); F2 = DevVec(nf)
+    check(lib().d4b_mg_prolong(T.handle, Cc.ptr, F2.ptr, None))
+    pf = F2.get()
+    assert rel(pf, so.transfer(tab, xc, nf, False)) < 1e-13
+    assert abs(pf @ xf - xc @ so.transfer(tab, xf, nc, True)) < 1e-10   # restriction = prolongation^T
+
+
+def test_mg_preconditioned_fcg_on_brick():
+    """BASELINE config 4 in miniature: MG (Chebyshev smoother + Chebyshev bottom solver) preconditioned
+    flexible CG to 1e-10; same iteration count (+-1) as the numpy restatement driving the same V-cycle."""
+    deg, levels = 2, [d4est_b200.MeshLevel.brick(2, deg=2), d4est_b200.MeshLevel.brick(4, deg=2), d4est_b200.MeshLevel.brick(8, deg=2)]
+    trs = [capi.Transfer(so.brick_transfer_table(2, deg)), capi.Transfer(so.brick_transfer_table(4, deg))]
+    mg = capi.Multigrid(levels, trs, cheby_imax=8, cheby_eigs_cg_imax=10, bottom_imax=10, bottom_eigs_cg_imax=10)
+    n = levels[-1].local_nodes
+    rhs = np.random.default_rng(11).standard_normal(n)
+    U, R, W = DevVec(n), DevVec(n, rhs), DevVec(6 * n)
+    it, res = C.c_int(), C.c_double()
+    check(lib().d4b_mg_fcg_solve(mg.handle, U.ptr, R.ptr, 100, 0., 1e-10, C.byref(it), C.byref(res), W.ptr, None))
+    u = U.get()
+    r = rhs - levels[-1].apply_host(u)
+    assert np.linalg.norm(r) <= 1e-9 * np.linalg.norm(rhs)
+    assert it.value < 30
+    # unpreconditioned CG needs many more iterations on the same system
+    U2 = DevVec(n); it2 = C.c_int()
+    check(lib().d4b_fcg_solve(levels[-1].handle, U2.ptr, R.ptr, 2000, 0., 1e-10, None, None, C.byref(it2), C.byref(res), W.ptr, None))
+    assert it2.value > 2 * it.value
