@@ -185,7 +185,7 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   cudaFree(m->deg); cudaFree(m->node_off); cudaFree(m->degq); cudaFree(m->quad_off); cudaFree(m->G);
   cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost);
   cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
-  for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); }
+  for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); cudaFree(m->fast[i].nrec); }
   cudaFree(m->generic_list);
   free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
   free(m->send_node_begin_h); free(m->recv_node_begin_h);
@@ -236,7 +236,19 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
 int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
 {
   const int nl = m->n_local;
-  std::vector<std::vector<int32_t>> el(D4B_NDEG * D4B_NDEGQ), fr(D4B_NDEG * D4B_NDEGQ);
+  std::vector<std::vector<int32_t>> el(D4B_NDEG * D4B_NDEGQ), fr(D4B_NDEG * D4B_NDEGQ), nr(D4B_NDEG * D4B_NDEGQ);
+  /* (element, face) -> its single conforming record, for the neighbour-record table of v3 */
+  std::vector<int32_t> rec_of;
+  if (D->hm) {
+    rec_of.assign((size_t)nl * 6, -1);
+    for (int e = 0; e < nl; e++)
+      for (int r = D->hm_begin[e]; r < D->hm_begin[e + 1]; r++) {
+        const d4b_hm_t &h = D->hm[r];
+        if (h.f_m < 0 || h.f_m > 5) continue;
+        int32_t &slot = rec_of[(size_t)e * 6 + h.f_m];
+        slot = (slot == -1 && h.child_m < 0 && h.child_p < 0) ? r : -3; /* -3: hanging / several records */
+      }
+  }
   std::vector<int32_t> gen;
   const bool off = getenv("D4B_NO_FAST") != nullptr;
   for (int e = 0; e < nl; e++) {
@@ -256,7 +268,17 @@ int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
     }
     if (!ok) { gen.push_back(e); continue; }
     int k = dg * D4B_NDEGQ + dq;
-    el[k].push_back(e); fr[k].insert(fr[k].end(), rec, rec + 6);
+    int32_t nrc[6];
+    for (int f = 0; f < 6; f++) {
+      if (!D->hm) { nrc[f] = -2; continue; } /* device-built brick: filled by d4b_brick_create */
+      const d4b_hm_t &h = D->hm[rec[f]];
+      nrc[f] = h.nbr < 0 ? -1 : -2;
+      if (h.nbr >= 0 && h.nbr < nl && h.f_p >= 0 && h.f_p < 6) {
+        int r2 = rec_of[(size_t)h.nbr * 6 + h.f_p];
+        if (r2 >= 0 && D->hm[r2].nbr == e && D->hm[r2].degq == h.degq && D->hm[r2].f_p == h.f_m) nrc[f] = r2;
+      }
+    }
+    el[k].push_back(e); fr[k].insert(fr[k].end(), rec, rec + 6); nr[k].insert(nr[k].end(), nrc, nrc + 6);
   }
   m->n_fast = 0;
   int64_t dummy = 0; int rc;
@@ -267,6 +289,8 @@ int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
     b.N = k / D4B_NDEGQ + 1; b.Nq = k % D4B_NDEGQ + 1; b.count = (int)el[k].size();
     if ((rc = upload(&b.elem_list, el[k].data(), el[k].size(), &dummy)) != D4B_OK) return rc;
     if ((rc = upload(&b.frec, fr[k].data(), fr[k].size(), &dummy)) != D4B_OK) return rc;
+    b.nrec = nullptr;
+    if ((rc = upload(&b.nrec, nr[k].data(), nr[k].size(), &dummy)) != D4B_OK) return rc;
   }
   m->n_generic = (int)gen.size();
   std::sort(gen.begin(), gen.end());

@@ -431,6 +431,11 @@ int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t
   *handled = 1;
   for (int i = 0; i < m->n_fast; i++) {
     const d4b_fast_bucket &b = m->fast[i];
+    if (b.nrec && d4b_v3_supported(b.N, b.Nq)) {
+      int rc3 = d4b_launch_v3(m, b, u, Au, st);
+      if (rc3 != D4B_OK) return rc3;
+      continue;
+    }
     int rc = upload_tab(m->quad_type, b.N, b.Nq, st);
     if (rc != D4B_OK) return rc;
     rc = D4B_EINVAL;

@@ -1,0 +1,654 @@
+/* d4b_apply_v3.cu -- register-blocked SIPG apply for "regular" elements (same element class as
+ * d4b_apply_fast.cu: every face a physical boundary or a conforming interface with an
+ * equal-(deg,deg_quad) neighbour, any inter-tree orientation).
+ *
+ * Formulation (same operator as dGMath/d4est_laplacian_with_opt.c:289, restated in the Lagrange
+ * basis ON the quadrature points, exact because deg_quad >= deg):
+ *     ut = (B x B x B) u                       interpolation GLL -> quad points
+ *     g_l = Dq_l ut                            collocated reference gradient
+ *     h   = G g                                metric (Quadrature/d4est_quadrature.c:339-375)
+ *     face trace of field x on face (d,+-) = sum_m e+-(m) x(..m..)   (rank-1 along the normal),
+ *     normal derivative = sum_m ed+-(m) ut(..m..), ed = Dq^T e
+ *     flux at mortar points as in ..._flux_sipg.c:645-677 (interior) / :139-191 (Dirichlet)
+ *     rt  = sum_l Dq_l^T (h_l + lift H_l) + lift F ;   Au = (B x B x B)^T rt
+ * Thread mapping: Nq threads per element, each holding one PLANE of the element in registers, in
+ * two layouts -- A: thread = r-index, plane (s,t);  C: thread = t-index, plane (r,s).  Two of the
+ * three contractions are register-local in each layout; the third moves through a per-warp
+ * shared-memory transposition (__syncwarp only, no block barriers).  Neighbour traces are built
+ * by one lane per face from the neighbour's nodal values, staged by cp.async.bulk + mbarrier; the
+ * neighbour-side factor a+ is read as -a- of the NEIGHBOUR's record (one copy in HBM per side).
+ */
+#include "d4b_internal.h"
+#include "d4b_ops.h"
+#include <cstdlib>
+#include <cstring>
+
+#define V3_MAXN 8
+#define V3_MAXQ 8
+struct v3_tab {
+  double B[V3_MAXQ * V3_MAXN];   /* Nq x N  GLL -> quad interpolation                 */
+  double Dq[V3_MAXQ * V3_MAXQ];  /* Nq x Nq derivative of the quad-point Lagrange basis */
+  double D[V3_MAXN * V3_MAXN];   /* N x N   GLL derivative (neighbour normal lines)    */
+  double e[2][V3_MAXQ];          /* quad-point basis at -1 / +1                        */
+  double ed[2][V3_MAXQ];         /* its derivative at -1 / +1  (= Dq^T e)              */
+  double w[V3_MAXQ];
+};
+__constant__ v3_tab c_v3;
+
+struct v3_args {
+  const int64_t *node_off; const int64_t *quad_off; const double *G; const d4b_hm_t *hm;
+  const double *fac; const double *bc_g; const double *u, *u_ghost; double *Au;
+  const int32_t *elem_list; const int32_t *frec; const int32_t *nrec; int n_list; int n_local;
+  int64_t local_nodes;
+};
+
+#define FULL 0xffffffffu
+
+/* ---- small dense contractions on register planes p[x + X*y] ------------------------------ */
+/* along x:  out[o + O*y] = sum_i M(o,i) in[i + I*y],  M(o,i) = TR ? M[i*O+o] : M[o*I+i]      */
+template <int I, int O, int Y, bool TR>
+__device__ __forceinline__ void cx(const double *M, const double (&in)[I * Y], double (&out)[O * Y])
+{
+#pragma unroll
+  for (int y = 0; y < Y; y++)
+#pragma unroll
+    for (int o = 0; o < O; o++) {
+      double s = 0.;
+#pragma unroll
+      for (int i = 0; i < I; i++) s = fma(TR ? M[i * O + o] : M[o * I + i], in[i + I * y], s);
+      out[o + O * y] = s;
+    }
+}
+/* along y:  out[x + X*o] = sum_i M(o,i) in[x + X*i] */
+template <int I, int O, int X, bool TR>
+__device__ __forceinline__ void cy(const double *M, const double (&in)[X * I], double (&out)[X * O])
+{
+#pragma unroll
+  for (int o = 0; o < O; o++)
+#pragma unroll
+    for (int x = 0; x < X; x++) {
+      double s = 0.;
+#pragma unroll
+      for (int i = 0; i < I; i++) s = fma(TR ? M[i * O + o] : M[o * I + i], in[x + X * i], s);
+      out[x + X * o] = s;
+    }
+}
+template <int I, int O, int X, bool TR>
+__device__ __forceinline__ void cy_acc(const double *M, const double (&in)[X * I], double (&out)[X * O])
+{
+#pragma unroll
+  for (int o = 0; o < O; o++)
+#pragma unroll
+    for (int x = 0; x < X; x++) {
+      double s = out[x + X * o];
+#pragma unroll
+      for (int i = 0; i < I; i++) s = fma(TR ? M[i * O + o] : M[o * I + i], in[x + X * i], s);
+      out[x + X * o] = s;
+    }
+}
+template <int I, int O, int Y, bool TR>
+__device__ __forceinline__ void cx_acc(const double *M, const double (&in)[I * Y], double (&out)[O * Y])
+{
+#pragma unroll
+  for (int y = 0; y < Y; y++)
+#pragma unroll
+    for (int o = 0; o < O; o++) {
+      double s = out[o + O * y];
+#pragma unroll
+      for (int i = 0; i < I; i++) s = fma(TR ? M[i * O + o] : M[o * I + i], in[i + I * y], s);
+      out[o + O * y] = s;
+    }
+}
+
+/* ---- mbarrier / bulk-copy PTX ------------------------------------------------------------ */
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(void *bar, int count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(void *bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void *bar, uint32_t parity)
+{
+  asm volatile(
+      "{\n .reg .pred p;\n WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra DONE_%=;\n bra WAIT_%=;\n DONE_%=:\n}\n" ::"r"(
+          smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, void *bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+template <int N, int Nq> struct V3 {
+  static constexpr int TPE = Nq, EPW = 32 / Nq, Q2 = Nq * Nq, Q3 = Q2 * Nq, N2 = N * N, N3 = N2 * N;
+  static constexpr int PSN = N2 + 1;                 /* padded nodal plane stride             */
+  static constexpr int PS = Q2 + 1;                  /* padded quad plane stride              */
+  static constexpr int ESN = ((N * PSN + 3) / 4) * 4;   /* nodal element stride (UB)           */
+  static constexpr int EST = ((Nq * PS + 3) / 4) * 4;   /* transposition-buffer element stride */
+  static constexpr int UBS = EPW * (ESN > EST ? ESN : EST); /* UB also parks a quad plane field */
+  static constexpr int TBS = EPW * EST;
+  static constexpr int HTS = EPW * 2 * Q2;
+  static constexpr int FAS = EPW * 6 * 2 * Q2;
+  static constexpr int TASKD = N3 + 3 * Q2;          /* doubles staged per neighbour face     */
+  static constexpr int SS = TASKD + (((TASKD / 2) % 2 == 0) ? 2 : 0); /* slot stride: SS/2 odd */
+  static constexpr int NSLOT = 4 * EPW;              /* round 0: faces 0..3, round 1: faces 4,5 */
+  static constexpr int NSS = NSLOT * SS;
+  static constexpr int PERWARP = UBS + 2 * TBS + HTS + FAS + NSS; /* doubles */
+  static constexpr int WPB_MAX = (227 * 1024 - 128) / (PERWARP * 8);
+  static constexpr int WPB = WPB_MAX >= 4 ? 4 : (WPB_MAX >= 1 ? WPB_MAX : 1);
+  static constexpr int THREADS = 32 * WPB;
+  static constexpr size_t SMEM = 128 + (size_t)WPB * PERWARP * 8;
+  static constexpr bool BULK = (N3 % 2 == 0) && (Q2 % 2 == 0);
+};
+
+/* my face point (ma,mb) -> index of the same physical point in the neighbour's face order
+ * (inverse of the map used by d4b_apply_fast.cu; tcode per include/d4est_b200.h) */
+template <int Nq> __device__ __forceinline__ int to_nbr_point(int tc, int ma, int mb)
+{
+  int xx = (tc & 1) ? ma : mb, yy = (tc & 1) ? mb : ma;
+  int qa = (tc & 2) ? Nq - 1 - xx : xx, qb = (tc & 4) ? Nq - 1 - yy : yy;
+  return qa + Nq * qb;
+}
+/* neighbour face point (qa,qb) -> index in MY face order */
+template <int Nq> __device__ __forceinline__ int to_my_point(int tc, int qa, int qb)
+{
+  int xx = (tc & 2) ? Nq - 1 - qa : qa, yy = (tc & 4) ? Nq - 1 - qb : qb;
+  return (tc & 1) ? xx + Nq * yy : yy + Nq * xx;
+}
+
+/* One lane builds the neighbour-side trace of one face from the staged slot S = { u_nbr[N^3],
+ * a[3][Nq^2] }:  out[q'] = u+ and out[Q2+q'] = sum_l a+_l du+/dr_l at the neighbour's face
+ * quadrature points q' (neighbour order).  mode 1: a = a- of the neighbour's own record (a+ = -a-,
+ * natural order);  mode 2: a = a+ stored in my record (my point order). */
+template <int N, int Nq>
+__device__ __forceinline__ void v3_nbr_trace(const double *S, int f_p, int tc, int mode, double *out)
+{
+  constexpr int N2 = N * N, N3 = N2 * N, Q2 = Nq * Nq;
+  const int dp = f_p >> 1;
+  const int sa = dp == 0 ? N : 1, sb = dp == 2 ? N : N2, sn = dp == 0 ? 1 : (dp == 1 ? N : N2);
+  const int lay = (f_p & 1) ? (N - 1) * sn : 0;
+  const double *Dl = c_v3.D + ((f_p & 1) ? (N - 1) * N : 0);
+  double X[N2], dn[N2];
+#pragma unroll
+  for (int xb = 0; xb < N; xb++)
+#pragma unroll
+    for (int xa = 0; xa < N; xa++) {
+      const double *p = S + xa * sa + xb * sb;
+      double s = 0.;
+#pragma unroll
+      for (int m = 0; m < N; m++) s = fma(Dl[m], p[m * sn], s);
+      dn[xa + N * xb] = s;
+      X[xa + N * xb] = p[lay];
+    }
+  double T1[Nq * N], U[Q2], DN[Q2], DA[Q2], DB[Q2];
+  cx<N, Nq, N, false>(c_v3.B, X, T1); cy<N, Nq, Nq, false>(c_v3.B, T1, U);
+  cx<N, Nq, N, false>(c_v3.B, dn, T1); cy<N, Nq, Nq, false>(c_v3.B, T1, DN);
+  cx<Nq, Nq, Nq, false>(c_v3.Dq, U, DA); cy<Nq, Nq, Nq, false>(c_v3.Dq, U, DB);
+  const double *An = S + N3;
+  const int ia = dp == 0 ? 1 : 0, ib = dp == 2 ? 1 : 2;
+  const double sgn = mode == 1 ? -1.0 : 1.0;
+#pragma unroll
+  for (int qb = 0; qb < Nq; qb++)
+#pragma unroll
+    for (int qa = 0; qa < Nq; qa++) {
+      const int q = qa + Nq * qb;
+      const int ix = mode == 1 ? q : to_my_point<Nq>(tc, qa, qb);
+      double v = An[ia * Q2 + ix] * DA[q] + An[ib * Q2 + ix] * DB[q] + An[dp * Q2 + ix] * DN[q];
+      out[q] = U[q];
+      out[Q2 + q] = sgn * v;
+    }
+}
+
+/* SIPG flux at the Nq face points a thread owns (…_flux_sipg.c:645-677, Dirichlet :139-191).
+ * Points i = 0..Nq-1 have face-local coordinates (ma,mb) = FIRST_FIXED ? (t,i) : (i,t).
+ * in: own trace ut and reference gradient (dr,ds,dt) at the points.
+ * out: F (tested with v), Hr/Hs/Ht (tested with dv/dr_l). */
+template <int Nq, bool FIRST_FIXED>
+__device__ __forceinline__ void v3_flux(const v3_args &A, const d4b_hm_t *h, const double *FAf, int t,
+                                        const double (&ut)[Nq], const double (&dr)[Nq], const double (&ds)[Nq],
+                                        const double (&dt)[Nq], double (&F)[Nq], double (&Hr)[Nq], double (&Hs)[Nq],
+                                        double (&Ht)[Nq])
+{
+  constexpr int Q2 = Nq * Nq;
+  const bool bnd = h->nbr < 0;
+  const int tc = h->tcode;
+  const double *Fp = A.fac + h->fac_off;
+  const int64_t goff = h->g_off;
+  const double wt = c_v3.w[t];
+#pragma unroll
+  for (int i = 0; i < Nq; i++) {
+    const int ma = FIRST_FIXED ? t : i, mb = FIRST_FIXED ? i : t;
+    const int q = ma + Nq * mb;
+    const double a0 = __ldg(Fp + q), a1 = __ldg(Fp + Q2 + q), a2 = __ldg(Fp + 2 * Q2 + q);
+    const double sjs = __ldg(Fp + (bnd ? 3 : 6) * Q2 + q);
+    const double w = wt * c_v3.w[i];
+    const double qm = a0 * dr[i] + a1 * ds[i] + a2 * dt[i];
+    double jump, t1, hs;
+    if (!bnd) {
+      const int qn = to_nbr_point<Nq>(tc, ma, mb);
+      jump = ut[i] - FAf[qn]; t1 = -0.5 * (qm + FAf[Q2 + qn]); hs = -0.5;
+    } else {
+      const double g = (goff >= 0) ? __ldg(A.bc_g + goff + q) : 0.;
+      jump = ut[i] - g; t1 = -qm; hs = -1.0;
+    }
+    F[i] = w * (t1 + sjs * jump);
+    const double c = w * hs * jump;
+    Hr[i] = c * a0; Hs[i] = c * a1; Ht[i] = c * a2;
+  }
+}
+
+template <int N, int Nq>
+__global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(const v3_args A)
+{
+  using L = V3<N, Nq>;
+  constexpr int TPE = L::TPE, EPW = L::EPW, Q2 = L::Q2, Q3 = L::Q3, N2 = L::N2, N3 = L::N3;
+  constexpr int PSN = L::PSN, PS = L::PS, ESN = L::ESN, EST = L::EST, SS = L::SS;
+  extern __shared__ __align__(128) unsigned char smraw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint64_t *bar = reinterpret_cast<uint64_t *>(smraw) + warp;
+  double *W = reinterpret_cast<double *>(smraw + 128) + (size_t)warp * L::PERWARP;
+  double *UB = W, *TBa = UB + L::UBS, *TBb = TBa + L::TBS, *HT = TBb + L::TBS, *FA = HT + L::HTS, *NS = FA + L::FAS;
+  const int le = lane / TPE, t = lane % TPE;
+  const int slot0 = (blockIdx.x * L::WPB + warp) * EPW;
+  const int slot = slot0 + le;
+  const bool act = le < EPW && slot < A.n_list;
+  const int e = act ? A.elem_list[slot] : 0;
+  const int64_t noff = act ? A.node_off[e] : -1;
+  const double *B = c_v3.B, *Dq = c_v3.Dq;
+
+  if (lane == 0) { mbar_init(bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncwarp();
+
+  /* ---- neighbour staging: round r covers faces [4r, 4r + nf), nf = 4 (r=0) or 2 (r=1) ---- */
+  int tk_fp = 0, tk_tc = 0, tk_mode = 0;   /* my task of the current round */
+  auto issue_round = [&](int r) {
+    const int nf = r == 0 ? 4 : 2;
+    const int tle = lane / nf, tf = 4 * r + lane % nf;
+    const int tslot = slot0 + tle;
+    tk_mode = 0;
+    uint32_t bytes = 0;
+    const double *su = nullptr, *sa = nullptr;
+    if (tle < EPW && tslot < A.n_list) {
+      const int rec = A.frec[6 * tslot + tf];
+      const int nr = A.nrec[6 * tslot + tf];
+      const d4b_hm_t *h = A.hm + rec;
+      const int nb = h->nbr;
+      if (nb >= 0) {
+        tk_fp = h->f_p; tk_tc = h->tcode; tk_mode = nr >= 0 ? 1 : 2;
+        su = (nb < A.n_local) ? A.u + A.node_off[nb] : A.u_ghost + (A.node_off[nb] - A.local_nodes);
+        sa = nr >= 0 ? A.fac + A.hm[nr].fac_off : A.fac + h->fac_off + 3 * Q2;
+        if (L::BULK && ((((uintptr_t)su) | ((uintptr_t)sa)) & 15) == 0) bytes = (N3 + 3 * Q2) * 8;
+      }
+    }
+    const uint32_t total = __reduce_add_sync(FULL, bytes);
+    if (lane == 0 && total) mbar_expect_tx(bar, total);
+    __syncwarp();
+    if (tk_mode) {
+      double *dst = NS + lane * SS;
+      if (bytes) {
+        bulk_g2s(dst, su, N3 * 8, bar);
+        bulk_g2s(dst + N3, sa, 3 * Q2 * 8, bar);
+      } else { /* unaligned source (odd sizes): plain copy by the owning lane */
+        for (int i = 0; i < N3; i++) dst[i] = __ldg(su + i);
+        for (int i = 0; i < 3 * Q2; i++) dst[N3 + i] = __ldg(sa + i);
+      }
+    }
+    return total;
+  };
+  auto run_round = [&](int r, uint32_t total, uint32_t parity) {
+    if (total) mbar_wait(bar, parity);
+    __syncwarp();
+    const int nf = r == 0 ? 4 : 2;
+    if (tk_mode) {
+      const int tle = lane / nf, tf = 4 * r + lane % nf;
+      v3_nbr_trace<N, Nq>(NS + lane * SS, tk_fp, tk_tc, tk_mode, FA + (tle * 6 + tf) * 2 * Q2);
+    }
+    __syncwarp();
+  };
+  uint32_t npar = 0;
+  uint32_t tot0 = issue_round(0);
+
+  /* ---- own u -> UB (padded), coalesced ---- */
+#pragma unroll 1
+  for (int ee = 0; ee < EPW; ee++) {
+    const int64_t base = __shfl_sync(FULL, noff, ee * TPE);
+    if (base >= 0)
+      for (int n = lane; n < N3; n += 32) UB[ee * ESN + n + n / N2] = __ldg(A.u + base + n);
+  }
+  __syncwarp();
+  double *UBe = UB + le * ESN, *TAe = TBa + le * EST, *TBe = TBb + le * EST;
+
+  /* P1 (layout C, nodal): thread k = t < N holds u(:,:,k); B_r, B_s in registers -> v(a,b,k) */
+  if (act && t < N) {
+    double X[N2], V1[Nq * N], V[Q2];
+#pragma unroll
+    for (int j = 0; j < N; j++)
+#pragma unroll
+      for (int i = 0; i < N; i++) X[i + N * j] = UBe[i + N * j + PSN * t];
+    cx<N, Nq, N, false>(B, X, V1); cy<N, Nq, Nq, false>(B, V1, V);
+#pragma unroll
+    for (int b = 0; b < Nq; b++)
+#pragma unroll
+      for (int a = 0; a < Nq; a++) TAe[a + Nq * b + PS * t] = V[a + Nq * b];
+  }
+  __syncwarp();
+  /* A0 (layout A): thread a = t holds (b,c); B_t -> ut; write ut (T2) and g_t (T3) */
+  {
+    double V[Nq * N], ut[Q2], gt[Q2];
+    if (act) {
+#pragma unroll
+      for (int k = 0; k < N; k++)
+#pragma unroll
+        for (int b = 0; b < Nq; b++) V[b + Nq * k] = TAe[t + Nq * b + PS * k];
+      cy<N, Nq, Nq, false>(B, V, ut);
+      cy<Nq, Nq, Nq, false>(Dq, ut, gt);
+    }
+    __syncwarp();
+    if (act) {
+#pragma unroll
+      for (int c = 0; c < Nq; c++)
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          TAe[t + Nq * b + PS * c] = ut[b + Nq * c];
+          TBe[t + Nq * b + PS * c] = gt[b + Nq * c];
+        }
+    }
+  }
+  __syncwarp();
+  run_round(0, tot0, npar); if (tot0) npar ^= 1;
+  uint32_t tot1 = issue_round(1);
+
+  /* C0 (layout C): thread c = t holds (a,b): g_r -> T4; faces 0,1 (normal r) */
+  {
+    double uC[Q2], gtC[Q2], gr[Q2], rC[Q2];
+    if (act) {
+#pragma unroll
+      for (int b = 0; b < Nq; b++)
+#pragma unroll
+        for (int a = 0; a < Nq; a++) { uC[a + Nq * b] = TAe[a + Nq * b + PS * t]; gtC[a + Nq * b] = TBe[a + Nq * b + PS * t]; }
+      cx<Nq, Nq, Nq, false>(Dq, uC, gr);
+    }
+    __syncwarp();
+    if (act) {
+#pragma unroll
+      for (int b = 0; b < Nq; b++)
+#pragma unroll
+        for (int a = 0; a < Nq; a++) { TBe[a + Nq * b + PS * t] = gr[a + Nq * b]; rC[a + Nq * b] = 0.; }
+#pragma unroll
+      for (int s = 0; s < 2; s++) {
+        double ut[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          double s0 = 0., s1 = 0., s2 = 0.;
+#pragma unroll
+          for (int a = 0; a < Nq; a++) {
+            s0 = fma(c_v3.e[s][a], uC[a + Nq * b], s0); s1 = fma(c_v3.ed[s][a], uC[a + Nq * b], s1);
+            s2 = fma(c_v3.e[s][a], gtC[a + Nq * b], s2);
+          }
+          ut[b] = s0; dr[b] = s1; dt[b] = s2;
+        }
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          double s0 = 0.;
+#pragma unroll
+          for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], ut[m], s0);
+          ds[b] = s0;
+        }
+        const d4b_hm_t *h = A.hm + A.frec[6 * slot + s];
+        v3_flux<Nq, false>(A, h, FA + (le * 6 + s) * 2 * Q2, t, ut, dr, ds, dt, F, Hr, Hs, Ht);
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          double s0 = F[b];
+#pragma unroll
+          for (int m = 0; m < Nq; m++) s0 = fma(Dq[m * Nq + b], Hs[m], s0);
+#pragma unroll
+          for (int a = 0; a < Nq; a++)
+            rC[a + Nq * b] = fma(c_v3.e[s][a], s0, fma(c_v3.ed[s][a], Hr[b], rC[a + Nq * b]));
+          HT[(le * 2 + s) * Q2 + b + Nq * t] = Ht[b];
+        }
+      }
+      /* park rC (layout C) in UB: read back by the same thread in C1 */
+#pragma unroll
+      for (int i = 0; i < Q2; i++) UB[le * L::UBS / EPW + i * TPE + t] = rC[i];
+    }
+  }
+  __syncwarp();
+  run_round(1, tot1, npar); if (tot1) npar ^= 1;
+
+  /* A1 (layout A): thread a = t holds (b,c): faces 2..5, metric, s/t transposed derivatives */
+  {
+    double rA[Q2];
+    if (act) {
+      double ut[Q2], gr[Q2], hrF[Q2];
+#pragma unroll
+      for (int c = 0; c < Nq; c++)
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          ut[b + Nq * c] = TAe[t + Nq * b + PS * c]; gr[b + Nq * c] = TBe[t + Nq * b + PS * c];
+          rA[b + Nq * c] = 0.; hrF[b + Nq * c] = 0.;
+        }
+#pragma unroll
+      for (int s = 0; s < 2; s++) { /* faces 2,3: normal s (index b); my points (a=t, c) */
+        double tr[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+#pragma unroll
+        for (int c = 0; c < Nq; c++) {
+          double s0 = 0., s1 = 0., s2 = 0.;
+#pragma unroll
+          for (int b = 0; b < Nq; b++) {
+            s0 = fma(c_v3.e[s][b], ut[b + Nq * c], s0); s1 = fma(c_v3.ed[s][b], ut[b + Nq * c], s1);
+            s2 = fma(c_v3.e[s][b], gr[b + Nq * c], s2);
+          }
+          tr[c] = s0; ds[c] = s1; dr[c] = s2;
+        }
+#pragma unroll
+        for (int c = 0; c < Nq; c++) {
+          double s0 = 0.;
+#pragma unroll
+          for (int m = 0; m < Nq; m++) s0 = fma(Dq[c * Nq + m], tr[m], s0);
+          dt[c] = s0;
+        }
+        const d4b_hm_t *h = A.hm + A.frec[6 * slot + 2 + s];
+        v3_flux<Nq, true>(A, h, FA + (le * 6 + 2 + s) * 2 * Q2, t, tr, dr, ds, dt, F, Hr, Hs, Ht);
+#pragma unroll
+        for (int c = 0; c < Nq; c++) {
+          double s0 = F[c];
+#pragma unroll
+          for (int m = 0; m < Nq; m++) s0 = fma(Dq[m * Nq + c], Ht[m], s0);
+#pragma unroll
+          for (int b = 0; b < Nq; b++) {
+            rA[b + Nq * c] = fma(c_v3.e[s][b], s0, fma(c_v3.ed[s][b], Hs[c], rA[b + Nq * c]));
+            hrF[b + Nq * c] = fma(c_v3.e[s][b], Hr[c], hrF[b + Nq * c]);
+          }
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < 2; s++) { /* faces 4,5: normal t (index c); my points (a=t, b) */
+        double tr[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          double s0 = 0., s1 = 0., s2 = 0.;
+#pragma unroll
+          for (int c = 0; c < Nq; c++) {
+            s0 = fma(c_v3.e[s][c], ut[b + Nq * c], s0); s1 = fma(c_v3.ed[s][c], ut[b + Nq * c], s1);
+            s2 = fma(c_v3.e[s][c], gr[b + Nq * c], s2);
+          }
+          tr[b] = s0; dt[b] = s1; dr[b] = s2;
+        }
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          double s0 = 0.;
+#pragma unroll
+          for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], tr[m], s0);
+          ds[b] = s0;
+        }
+        const d4b_hm_t *h = A.hm + A.frec[6 * slot + 4 + s];
+        v3_flux<Nq, true>(A, h, FA + (le * 6 + 4 + s) * 2 * Q2, t, tr, dr, ds, dt, F, Hr, Hs, Ht);
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          double s0 = F[b];
+#pragma unroll
+          for (int m = 0; m < Nq; m++) s0 = fma(Dq[m * Nq + b], Hs[m], s0);
+#pragma unroll
+          for (int c = 0; c < Nq; c++) {
+            rA[b + Nq * c] = fma(c_v3.e[s][c], s0, fma(c_v3.ed[s][c], Ht[b], rA[b + Nq * c]));
+            hrF[b + Nq * c] = fma(c_v3.e[s][c], Hr[b], hrF[b + Nq * c]);
+          }
+        }
+      }
+      /* metric: h = G g at my points (a=t,b,c); h_t also receives the lift of faces 0,1 */
+      double gs[Q2], gt[Q2];
+      cx<Nq, Nq, Nq, false>(Dq, ut, gs); cy<Nq, Nq, Nq, false>(Dq, ut, gt);
+      const double *Ge = A.G + 6 * A.quad_off[e] + t;
+      const double e0 = c_v3.e[0][t], e1 = c_v3.e[1][t];
+      const double *HTe = HT + le * 2 * Q2;
+#pragma unroll
+      for (int c = 0; c < Nq; c++)
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          const int i = b + Nq * c, q = Nq * i;
+          const double G0 = __ldg(Ge + q), G1 = __ldg(Ge + Q3 + q), G2 = __ldg(Ge + 2 * Q3 + q),
+                       G3 = __ldg(Ge + 3 * Q3 + q), G4 = __ldg(Ge + 4 * Q3 + q), G5 = __ldg(Ge + 5 * Q3 + q);
+          const double a = gr[i], bb = gs[i], cc = gt[i];
+          gr[i] = G0 * a + G1 * bb + G2 * cc + hrF[i];
+          gs[i] = G1 * a + G3 * bb + G4 * cc;
+          gt[i] = G2 * a + G4 * bb + G5 * cc + e0 * HTe[i] + e1 * HTe[Q2 + i];
+        }
+      cx_acc<Nq, Nq, Nq, true>(Dq, gs, rA); cy_acc<Nq, Nq, Nq, true>(Dq, gt, rA);
+      /* h_r -> T5 (same addresses this thread read ut from) */
+#pragma unroll
+      for (int c = 0; c < Nq; c++)
+#pragma unroll
+        for (int b = 0; b < Nq; b++) TAe[t + Nq * b + PS * c] = gr[b + Nq * c];
+    }
+    __syncwarp();
+    /* C1 (layout C): rC += Dq_r^T h_r ; rC -> T7 */
+    if (act) {
+      double hr[Q2], rC[Q2];
+#pragma unroll
+      for (int b = 0; b < Nq; b++)
+#pragma unroll
+        for (int a = 0; a < Nq; a++) hr[a + Nq * b] = TAe[a + Nq * b + PS * t];
+#pragma unroll
+      for (int i = 0; i < Q2; i++) rC[i] = UB[le * L::UBS / EPW + i * TPE + t];
+      cx_acc<Nq, Nq, Nq, true>(Dq, hr, rC);
+#pragma unroll
+      for (int b = 0; b < Nq; b++)
+#pragma unroll
+        for (int a = 0; a < Nq; a++) TBe[a + Nq * b + PS * t] = rC[a + Nq * b];
+    }
+    __syncwarp();
+    /* A2 (layout A): rt = rA + rC ; B_t^T, B_s^T in registers -> y(a; j,k) -> T8 */
+    if (act) {
+      double Y1[Nq * N], Y[N2];
+#pragma unroll
+      for (int c = 0; c < Nq; c++)
+#pragma unroll
+        for (int b = 0; b < Nq; b++) rA[b + Nq * c] += TBe[t + Nq * b + PS * c];
+      cy<Nq, N, Nq, true>(B, rA, Y1);   /* contract c -> k : Y1[b + Nq k] */
+      cx<Nq, N, N, true>(B, Y1, Y);     /* contract b -> j : Y[j + N k]   */
+#pragma unroll
+      for (int k = 0; k < N; k++)
+#pragma unroll
+        for (int j = 0; j < N; j++) TAe[t + Nq * j + PS * k] = Y[j + N * k];
+    }
+  }
+  __syncwarp();
+  /* C2 (layout C, nodal): thread k = t < N: B_r^T -> Au(i,j,k) -> UB (padded) */
+  if (act && t < N) {
+    double Yc[Nq * N], O[N2];
+#pragma unroll
+    for (int j = 0; j < N; j++)
+#pragma unroll
+      for (int a = 0; a < Nq; a++) Yc[a + Nq * j] = TAe[a + Nq * j + PS * t];
+    cx<Nq, N, N, true>(B, Yc, O);
+#pragma unroll
+    for (int j = 0; j < N; j++)
+#pragma unroll
+      for (int i = 0; i < N; i++) UBe[i + N * j + PSN * t] = O[i + N * j];
+  }
+  __syncwarp();
+#pragma unroll 1
+  for (int ee = 0; ee < EPW; ee++) {
+    const int64_t base = __shfl_sync(FULL, noff, ee * TPE);
+    if (base >= 0)
+      for (int n = lane; n < N3; n += 32) A.Au[base + n] = UB[ee * ESN + n + n / N2];
+  }
+}
+
+/* ------------------------------------------------------------------ host side */
+#define V3_PAIRS(X) X(2, 2) X(2, 4) X(4, 4)
+
+bool d4b_v3_supported(int N, int Nq)
+{
+  static int off = -1;
+  if (off < 0) off = getenv("D4B_NO_V3") != nullptr;
+  if (off) return false;
+#define X(a, b) if (N == a && Nq == b) return true;
+  V3_PAIRS(X)
+#undef X
+  return false;
+}
+
+static int v3_upload_tab(int qt, int N, int Nq, cudaStream_t st)
+{
+  static int cur_qt = -1, cur_N = -1, cur_Nq = -1;
+  static v3_tab *h = nullptr;
+  static int ring = 0;
+  if (cur_qt == qt && cur_N == N && cur_Nq == Nq) return D4B_OK;
+  if (!h) D4B_CUDA(cudaMallocHost((void **)&h, 4 * sizeof(v3_tab)));
+  v3_tab *t = h + (ring++ & 3);
+  memset(t, 0, sizeof *t);
+  double I[D4B_OPS_MAXN * D4B_OPS_MAXN], Dm[D4B_OPS_MAXN * D4B_OPS_MAXN], Dqm[D4B_OPS_MAXN * D4B_OPS_MAXN];
+  double x[D4B_OPS_MAXN], w[D4B_OPS_MAXN], e0[D4B_OPS_MAXN], e1[D4B_OPS_MAXN];
+  d4b_ops_interp(N - 1, Nq - 1, qt, -1, I); d4b_ops_diff(N - 1, Dm); d4b_ops_quad(Nq - 1, qt, x, w);
+  d4b_ops_quadbasis(Nq - 1, qt, Dqm, e0, e1);
+  for (int i = 0; i < Nq * N; i++) t->B[i] = I[i];
+  for (int i = 0; i < Nq * Nq; i++) t->Dq[i] = Dqm[i];
+  for (int i = 0; i < N * N; i++) t->D[i] = Dm[i];
+  for (int m = 0; m < Nq; m++) {
+    t->e[0][m] = e0[m]; t->e[1][m] = e1[m]; t->w[m] = w[m];
+    double s0 = 0., s1 = 0.;
+    for (int a = 0; a < Nq; a++) { s0 += e0[a] * Dqm[a * Nq + m]; s1 += e1[a] * Dqm[a * Nq + m]; }
+    t->ed[0][m] = s0; t->ed[1][m] = s1;
+  }
+  D4B_CUDA(cudaMemcpyToSymbolAsync(c_v3, t, sizeof(v3_tab), 0, cudaMemcpyHostToDevice, st));
+  cur_qt = qt; cur_N = N; cur_Nq = Nq;
+  return D4B_OK;
+}
+
+template <int N, int Nq>
+static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st)
+{
+  using L = V3<N, Nq>;
+  static bool attr = false;
+  if (!attr) {
+    D4B_CUDA(cudaFuncSetAttribute(d4b_apply_v3_kernel<N, Nq>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM));
+    attr = true;
+  }
+  v3_args A;
+  A.node_off = m->node_off; A.quad_off = m->quad_off; A.G = m->G; A.hm = m->hm; A.fac = m->fac; A.bc_g = m->bc_g;
+  A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.elem_list = b.elem_list; A.frec = b.frec; A.nrec = b.nrec;
+  A.n_list = b.count; A.n_local = m->n_local; A.local_nodes = m->local_nodes;
+  const int per = L::EPW * L::WPB;
+  d4b_apply_v3_kernel<N, Nq><<<(b.count + per - 1) / per, L::THREADS, L::SMEM, st>>>(A);
+  D4B_CUDA(cudaGetLastError());
+  d4b_count_launch(1);
+  return D4B_OK;
+}
+
+int d4b_launch_v3(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st)
+{
+  int rc = v3_upload_tab(m->quad_type, b.N, b.Nq, st);
+  if (rc != D4B_OK) return rc;
+#define X(a, c) if (b.N == a && b.Nq == c) return v3_launch_t<a, c>(m, b, u, Au, st);
+  V3_PAIRS(X)
+#undef X
+  d4b_set_error("d4b_launch_v3: unsupported (N,Nq)"); return D4B_EINVAL;
+}

@@ -59,6 +59,16 @@ __global__ void brick_fill_faces(brick_dev B, d4b_hm_t *__restrict__ hm, double 
   }
 }
 
+/* neighbour-record table of the register-blocked kernel: records are in face order (6 e + f) and
+ * the single bucket lists the elements in order, so the neighbour's record of my face f is 6 nbr + (f^1) */
+__global__ void brick_fill_nrec(int n6, const d4b_hm_t *__restrict__ hm, int32_t *__restrict__ nrec)
+{
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n6) return;
+  int nb = hm[t].nbr;
+  nrec[t] = nb < 0 ? -1 : 6 * nb + ((t % 6) ^ 1);
+}
+
 static inline uint64_t morton3(uint32_t x, uint32_t y, uint32_t z)
 {
   uint64_t k = 0;
@@ -115,6 +125,8 @@ extern "C" int d4b_brick_create(const d4b_brick_params_t *p, d4b_mesh_t **out)
   int64_t nq = ne * Nq * Nq * Nq;
   brick_fill_G<<<(unsigned)((nq + 255) / 256), 256>>>(B, d_w, m->G);
   brick_fill_faces<<<(unsigned)((ne * 6 + 127) / 128), 128>>>(B, m->hm, m->fac);
+  if (m->n_fast == 1 && m->fast[0].count == ne && m->fast[0].nrec)
+    brick_fill_nrec<<<(unsigned)((ne * 6 + 255) / 256), 256>>>((int)(ne * 6), m->hm, m->fast[0].nrec);
   D4B_CUDA(cudaGetLastError());
   D4B_CUDA(cudaDeviceSynchronize());
   cudaFree(d_emap); cudaFree(d_ecoord); cudaFree(d_w);

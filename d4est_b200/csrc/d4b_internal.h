@@ -26,6 +26,8 @@ struct d4b_fast_bucket {
   int N, Nq, count;
   int32_t *elem_list;   /* device: element ids                                          */
   int32_t *frec;        /* device: [count][6] half-mortar record index of face f        */
+  int32_t *nrec;        /* device: [count][6] record of the NEIGHBOUR for the same face (its a- is my
+                           -a+), -1 boundary, -2 none (ghost / not mirrored: use my own a+)   */
 };
 #define D4B_MAX_BUCKETS 32
 
@@ -51,6 +53,8 @@ void d4b_set_error(const char *fmt, ...);
 const d4b_ops_dev *d4b_ops_device(int quad_type); /* lazily built + uploaded */
 void d4b_count_launch(int n);
 bool d4b_fast_supported(int N, int Nq);
+bool d4b_v3_supported(int N, int Nq);
+int d4b_launch_v3(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st);
 /* split elements into fast buckets + generic list; D->hm == NULL means the uniform device-built brick */
 int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D);
 

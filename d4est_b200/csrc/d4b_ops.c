@@ -139,3 +139,23 @@ void d4b_ops_prolong(int degH, int degh, int child, double *P)
     lagrange_row(NH, xH, lam, yy, &P[i * NH]);
   }
 }
+
+/* Lagrange basis ON the quadrature points (valid representation of a degree-deg polynomial
+ * whenever degq >= deg): Dq[a*Nq+m] = l~_m'(y_a), e0[m] = l~_m(-1), e1[m] = l~_m(+1).
+ * Used by the register-blocked kernel (d4b_apply_v3.cu): face traces and lifts become
+ * rank-1 operations along the face normal. */
+void d4b_ops_quadbasis(int degq, int quad_type, double *Dq, double *e0, double *e1)
+{
+  int Nq = degq + 1; double y[D4B_OPS_MAXN], wy[D4B_OPS_MAXN]; ld lam[D4B_OPS_MAXN];
+  d4b_ops_quad(degq, quad_type, y, wy); bary_weights(Nq, y, lam);
+  for (int i = 0; i < Nq; i++) {
+    ld s = 0.0L;
+    for (int j = 0; j < Nq; j++) if (j != i) {
+      ld v = (lam[j] / lam[i]) / ((ld)y[i] - (ld)y[j]);
+      Dq[i * Nq + j] = (double)v; s += v;
+    }
+    Dq[i * Nq + i] = (double)(-s);
+  }
+  lagrange_row(Nq, y, lam, -1.0L, e0);
+  lagrange_row(Nq, y, lam, 1.0L, e1);
+}

@@ -11,6 +11,7 @@ void d4b_ops_quad(int degq, int quad_type, double *x, double *w);
 void d4b_ops_diff(int deg, double *D);
 void d4b_ops_interp(int deg, int degq, int quad_type, int child, double *I);
 void d4b_ops_prolong(int degH, int degh, int child, double *P);
+void d4b_ops_quadbasis(int degq, int quad_type, double *Dq, double *e0, double *e1);
 #ifdef __cplusplus
 }
 #endif
