@@ -185,7 +185,7 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   cudaFree(m->deg); cudaFree(m->node_off); cudaFree(m->degq); cudaFree(m->quad_off); cudaFree(m->G);
   cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost);
   cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
-  for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); cudaFree(m->fast[i].nrec); }
+  for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); cudaFree(m->fast[i].nrec); cudaFree(m->fast[i].v3_slots); }
   cudaFree(m->generic_list);
   free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
   free(m->send_node_begin_h); free(m->recv_node_begin_h);
@@ -289,7 +289,7 @@ int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
     b.N = k / D4B_NDEGQ + 1; b.Nq = k % D4B_NDEGQ + 1; b.count = (int)el[k].size();
     if ((rc = upload(&b.elem_list, el[k].data(), el[k].size(), &dummy)) != D4B_OK) return rc;
     if ((rc = upload(&b.frec, fr[k].data(), fr[k].size(), &dummy)) != D4B_OK) return rc;
-    b.nrec = nullptr;
+    b.nrec = nullptr; b.v3_slots = nullptr;
     if ((rc = upload(&b.nrec, nr[k].data(), nr[k].size(), &dummy)) != D4B_OK) return rc;
   }
   m->n_generic = (int)gen.size();

@@ -35,14 +35,8 @@ struct v3_tab {
 };
 __constant__ v3_tab c_v3;
 
-struct v3_args {
-  const int64_t *node_off; const int64_t *quad_off; const double *G; const d4b_hm_t *hm;
-  const double *fac; const double *bc_g; const double *u, *u_ghost; double *Au;
-  const int32_t *elem_list; const int32_t *frec; const int32_t *nrec; int n_list; int n_local;
-  int64_t local_nodes;
-};
-
 #define FULL 0xffffffffu
+
 
 /* ---- small dense contractions on register planes p[x + X*y] ------------------------------ */
 /* along x:  out[o + O*y] = sum_i M(o,i) in[i + I*y],  M(o,i) = TR ? M[i*O+o] : M[o*I+i]      */
@@ -126,26 +120,76 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
                : "memory");
 }
 
+/* Per-slot metadata, resolved once per bucket (v3_build_slots): one coalesced read per element
+ * instead of the frec -> hm -> node_off pointer chase. */
+struct v3_face {
+  int64_t fac_off;   /* my record: a-[3][Q2] at +0, sj*sigma at +6 Q2 (interior) / +3 Q2 (boundary) */
+  int64_t g_off;     /* Dirichlet data offset or -1                                               */
+  int64_t nbr_u;     /* >= 0: offset into u;  < 0: -(offset into u_ghost) - 1                      */
+  int64_t nbr_a;     /* offset into fac of the 3 Q2 doubles folded with the neighbour gradient     */
+  int32_t code;      /* bits 0-2 tcode, 3-5 f_p, 6-7 mode: 0 boundary, 1 nbr a- (a+ = -a-), 2 own a+ */
+  int32_t pad;
+};
+struct v3_slot { int64_t node_off, quad_off; v3_face f[6]; };   /* 256 bytes */
+
+__global__ void v3_build_slots(int n, const int32_t *__restrict__ elem_list, const int32_t *__restrict__ frec,
+                               const int32_t *__restrict__ nrec, const d4b_hm_t *__restrict__ hm,
+                               const int64_t *__restrict__ node_off, const int64_t *__restrict__ quad_off,
+                               int n_local, int64_t local_nodes, int Q2, v3_slot *__restrict__ out)
+{
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const int e = elem_list[s];
+  v3_slot S;
+  S.node_off = node_off[e]; S.quad_off = quad_off[e];
+  for (int f = 0; f < 6; f++) {
+    const d4b_hm_t h = hm[frec[6 * s + f]];
+    const int nr = nrec[6 * s + f];
+    v3_face F;
+    F.fac_off = h.fac_off; F.g_off = h.g_off; F.nbr_u = 0; F.nbr_a = 0; F.pad = 0;
+    int mode = 0;
+    if (h.nbr >= 0) {
+      mode = nr >= 0 ? 1 : 2;
+      F.nbr_u = h.nbr < n_local ? node_off[h.nbr] : -(node_off[h.nbr] - local_nodes) - 1;
+      F.nbr_a = nr >= 0 ? hm[nr].fac_off : h.fac_off + 3 * Q2;
+    }
+    F.code = (h.tcode & 7) | ((h.f_p & 7) << 3) | (mode << 6);
+    S.f[f] = F;
+  }
+  out[s] = S;
+}
+
+struct v3_args {
+  const v3_slot *slots; const double *G; const double *fac; const double *bc_g;
+  const double *u, *u_ghost; double *Au; int n_list;
+};
+
 template <int N, int Nq> struct V3 {
   static constexpr int TPE = Nq, EPW = 32 / Nq, Q2 = Nq * Nq, Q3 = Q2 * Nq, N2 = N * N, N3 = N2 * N;
-  static constexpr int PSN = N2 + 1;                 /* padded nodal plane stride             */
-  static constexpr int PS = Q2 + 1;                  /* padded quad plane stride              */
-  static constexpr int ESN = ((N * PSN + 3) / 4) * 4;   /* nodal element stride (UB)           */
-  static constexpr int EST = ((Nq * PS + 3) / 4) * 4;   /* transposition-buffer element stride */
-  static constexpr int UBS = EPW * (ESN > EST ? ESN : EST); /* UB also parks a quad plane field */
-  static constexpr int TBS = EPW * EST;
+  static constexpr bool SWZ = (N == 4 && Nq == 4);   /* XOR-swizzled 64-double element blocks      */
+  static constexpr int PS = Q2 + 1;                  /* padded plane stride (generic layout)       */
+  static constexpr int EST = SWZ ? 64 : ((Nq * PS + 3) / 4) * 4; /* element stride of X/Y/Z buffers */
+  static constexpr int BUF = EPW * EST;
   static constexpr int HTS = EPW * 2 * Q2;
-  static constexpr int FAS = EPW * 6 * 2 * Q2;
-  static constexpr int TASKD = N3 + 3 * Q2;          /* doubles staged per neighbour face     */
-  static constexpr int SS = TASKD + (((TASKD / 2) % 2 == 0) ? 2 : 0); /* slot stride: SS/2 odd */
-  static constexpr int NSLOT = 4 * EPW;              /* round 0: faces 0..3, round 1: faces 4,5 */
+  static constexpr int FS = 2 * Q2 + 1;              /* stride of one neighbour-trace pair in FA   */
+  static constexpr int FAS = ((EPW * 4 * FS + 3) / 4) * 4;   /* faces 2..5                         */
+  static constexpr int TASKD = N3 + 3 * Q2;          /* doubles staged per neighbour face          */
+  static constexpr int SS = TASKD + (((TASKD / 2) % 2 == 0) ? 2 : 0) + (TASKD % 2); /* even, SS/2 odd */
+  static constexpr int NSLOT = 2 * EPW;              /* one round = faces 2r, 2r+1 of all elements */
   static constexpr int NSS = NSLOT * SS;
-  static constexpr int PERWARP = UBS + 2 * TBS + HTS + FAS + NSS; /* doubles */
-  static constexpr int WPB_MAX = (227 * 1024 - 128) / (PERWARP * 8);
-  static constexpr int WPB = WPB_MAX >= 4 ? 4 : (WPB_MAX >= 1 ? WPB_MAX : 1);
+  static constexpr int PERWARP = 3 * BUF + HTS + FAS + NSS + 2; /* doubles; +2: mbarrier          */
+  static constexpr int WPB_MAX = (227 * 1024) / (PERWARP * 8);
+  static constexpr int WPB = WPB_MAX >= 6 ? 6 : (WPB_MAX >= 1 ? WPB_MAX : 1);
   static constexpr int THREADS = 32 * WPB;
-  static constexpr size_t SMEM = 128 + (size_t)WPB * PERWARP * 8;
+  static constexpr size_t SMEM = (size_t)WPB * PERWARP * 8;
   static constexpr bool BULK = (N3 % 2 == 0) && (Q2 % 2 == 0);
+  /* index of (a,b,c) inside the element block of a transposition buffer.  Swizzled form: both the
+   * layout-A access (lanes vary a and element) and the layout-C access (lanes vary c and element)
+   * touch 16 distinct 8-byte bank pairs per half-warp. */
+  static __device__ __forceinline__ int ti(int a, int b, int c, int le)
+  {
+    return SWZ ? ((a ^ c) + 4 * (b ^ (le & 3)) + 16 * c) : (a + Nq * b + PS * c);
+  }
 };
 
 /* my face point (ma,mb) -> index of the same physical point in the neighbour's face order
@@ -166,7 +210,7 @@ template <int Nq> __device__ __forceinline__ int to_my_point(int tc, int qa, int
 /* One lane builds the neighbour-side trace of one face from the staged slot S = { u_nbr[N^3],
  * a[3][Nq^2] }:  out[q'] = u+ and out[Q2+q'] = sum_l a+_l du+/dr_l at the neighbour's face
  * quadrature points q' (neighbour order).  mode 1: a = a- of the neighbour's own record (a+ = -a-,
- * natural order);  mode 2: a = a+ stored in my record (my point order). */
+ * natural order);  mode 2: a = a+ stored in my record (my point order).  out may alias S. */
 template <int N, int Nq>
 __device__ __forceinline__ void v3_nbr_trace(const double *S, int f_p, int tc, int mode, double *out)
 {
@@ -175,72 +219,103 @@ __device__ __forceinline__ void v3_nbr_trace(const double *S, int f_p, int tc, i
   const int sa = dp == 0 ? N : 1, sb = dp == 2 ? N : N2, sn = dp == 0 ? 1 : (dp == 1 ? N : N2);
   const int lay = (f_p & 1) ? (N - 1) * sn : 0;
   const double *Dl = c_v3.D + ((f_p & 1) ? (N - 1) * N : 0);
-  double X[N2], dn[N2];
+  double U[Q2], Qv[Q2];
+  {
+    double X[N2], T1[Nq * N];
 #pragma unroll
-  for (int xb = 0; xb < N; xb++)
+    for (int xb = 0; xb < N; xb++)
 #pragma unroll
-    for (int xa = 0; xa < N; xa++) {
-      const double *p = S + xa * sa + xb * sb;
-      double s = 0.;
-#pragma unroll
-      for (int m = 0; m < N; m++) s = fma(Dl[m], p[m * sn], s);
-      dn[xa + N * xb] = s;
-      X[xa + N * xb] = p[lay];
-    }
-  double T1[Nq * N], U[Q2], DN[Q2], DA[Q2], DB[Q2];
-  cx<N, Nq, N, false>(c_v3.B, X, T1); cy<N, Nq, Nq, false>(c_v3.B, T1, U);
-  cx<N, Nq, N, false>(c_v3.B, dn, T1); cy<N, Nq, Nq, false>(c_v3.B, T1, DN);
-  cx<Nq, Nq, Nq, false>(c_v3.Dq, U, DA); cy<Nq, Nq, Nq, false>(c_v3.Dq, U, DB);
+      for (int xa = 0; xa < N; xa++) X[xa + N * xb] = S[xa * sa + xb * sb + lay];
+    cx<N, Nq, N, false>(c_v3.B, X, T1); cy<N, Nq, Nq, false>(c_v3.B, T1, U);
+  }
   const double *An = S + N3;
   const int ia = dp == 0 ? 1 : 0, ib = dp == 2 ? 1 : 2;
+  {
+    double DA[Q2], DB[Q2];
+    cx<Nq, Nq, Nq, false>(c_v3.Dq, U, DA); cy<Nq, Nq, Nq, false>(c_v3.Dq, U, DB);
+#pragma unroll
+    for (int qb = 0; qb < Nq; qb++)
+#pragma unroll
+      for (int qa = 0; qa < Nq; qa++) {
+        const int q = qa + Nq * qb;
+        const int ix = mode == 1 ? q : to_my_point<Nq>(tc, qa, qb);
+        Qv[q] = An[ia * Q2 + ix] * DA[q] + An[ib * Q2 + ix] * DB[q];
+      }
+  }
+  {
+    double dn[N2], T1[Nq * N], DN[Q2];
+#pragma unroll
+    for (int xb = 0; xb < N; xb++)
+#pragma unroll
+      for (int xa = 0; xa < N; xa++) {
+        const double *p = S + xa * sa + xb * sb;
+        double s = 0.;
+#pragma unroll
+        for (int m = 0; m < N; m++) s = fma(Dl[m], p[m * sn], s);
+        dn[xa + N * xb] = s;
+      }
+    cx<N, Nq, N, false>(c_v3.B, dn, T1); cy<N, Nq, Nq, false>(c_v3.B, T1, DN);
+#pragma unroll
+    for (int qb = 0; qb < Nq; qb++)
+#pragma unroll
+      for (int qa = 0; qa < Nq; qa++) {
+        const int q = qa + Nq * qb;
+        const int ix = mode == 1 ? q : to_my_point<Nq>(tc, qa, qb);
+        Qv[q] = fma(An[dp * Q2 + ix], DN[q], Qv[q]);
+      }
+  }
   const double sgn = mode == 1 ? -1.0 : 1.0;
 #pragma unroll
-  for (int qb = 0; qb < Nq; qb++)
-#pragma unroll
-    for (int qa = 0; qa < Nq; qa++) {
-      const int q = qa + Nq * qb;
-      const int ix = mode == 1 ? q : to_my_point<Nq>(tc, qa, qb);
-      double v = An[ia * Q2 + ix] * DA[q] + An[ib * Q2 + ix] * DB[q] + An[dp * Q2 + ix] * DN[q];
-      out[q] = U[q];
-      out[Q2 + q] = sgn * v;
-    }
+  for (int q = 0; q < Q2; q++) { out[q] = U[q]; out[Q2 + q] = sgn * Qv[q]; }
 }
 
 /* SIPG flux at the Nq face points a thread owns (…_flux_sipg.c:645-677, Dirichlet :139-191).
  * Points i = 0..Nq-1 have face-local coordinates (ma,mb) = FIRST_FIXED ? (t,i) : (i,t).
- * in: own trace ut and reference gradient (dr,ds,dt) at the points.
+ * a[4][Nq]: a-_r, a-_s, a-_t, sj*sigma at the points (loaded by the caller ahead of use).
+ * in: own trace ut and reference gradient (dr,ds,dt);  NB: neighbour trace pair (u+ at +0, q+ at +Q2).
  * out: F (tested with v), Hr/Hs/Ht (tested with dv/dr_l). */
 template <int Nq, bool FIRST_FIXED>
-__device__ __forceinline__ void v3_flux(const v3_args &A, const d4b_hm_t *h, const double *FAf, int t,
-                                        const double (&ut)[Nq], const double (&dr)[Nq], const double (&ds)[Nq],
-                                        const double (&dt)[Nq], double (&F)[Nq], double (&Hr)[Nq], double (&Hs)[Nq],
-                                        double (&Ht)[Nq])
+__device__ __forceinline__ void v3_flux(const v3_args &A, int code, int64_t g_off, const double *NB, int t,
+                                        const double (&a)[4][Nq], const double (&ut)[Nq], const double (&dr)[Nq],
+                                        const double (&ds)[Nq], const double (&dt)[Nq], double (&F)[Nq],
+                                        double (&Hr)[Nq], double (&Hs)[Nq], double (&Ht)[Nq])
 {
   constexpr int Q2 = Nq * Nq;
-  const bool bnd = h->nbr < 0;
-  const int tc = h->tcode;
-  const double *Fp = A.fac + h->fac_off;
-  const int64_t goff = h->g_off;
+  const bool bnd = (code >> 6) == 0;
+  const int tc = code & 7;
   const double wt = c_v3.w[t];
 #pragma unroll
   for (int i = 0; i < Nq; i++) {
     const int ma = FIRST_FIXED ? t : i, mb = FIRST_FIXED ? i : t;
-    const int q = ma + Nq * mb;
-    const double a0 = __ldg(Fp + q), a1 = __ldg(Fp + Q2 + q), a2 = __ldg(Fp + 2 * Q2 + q);
-    const double sjs = __ldg(Fp + (bnd ? 3 : 6) * Q2 + q);
     const double w = wt * c_v3.w[i];
-    const double qm = a0 * dr[i] + a1 * ds[i] + a2 * dt[i];
+    const double qm = a[0][i] * dr[i] + a[1][i] * ds[i] + a[2][i] * dt[i];
     double jump, t1, hs;
     if (!bnd) {
       const int qn = to_nbr_point<Nq>(tc, ma, mb);
-      jump = ut[i] - FAf[qn]; t1 = -0.5 * (qm + FAf[Q2 + qn]); hs = -0.5;
+      jump = ut[i] - NB[qn]; t1 = -0.5 * (qm + NB[Q2 + qn]); hs = -0.5;
     } else {
-      const double g = (goff >= 0) ? __ldg(A.bc_g + goff + q) : 0.;
+      const double g = (g_off >= 0) ? __ldg(A.bc_g + g_off + ma + Nq * mb) : 0.;
       jump = ut[i] - g; t1 = -qm; hs = -1.0;
     }
-    F[i] = w * (t1 + sjs * jump);
+    F[i] = w * (t1 + a[3][i] * jump);
     const double c = w * hs * jump;
-    Hr[i] = c * a0; Hs[i] = c * a1; Ht[i] = c * a2;
+    Hr[i] = c * a[0][i]; Hs[i] = c * a[1][i]; Ht[i] = c * a[2][i];
+  }
+}
+/* the 4 x Nq own-side factors of a face at my points: issued early so the loads overlap the traces */
+template <int Nq, bool FIRST_FIXED>
+__device__ __forceinline__ void v3_load_fac(const v3_args &A, const v3_face *fc, int t, double (&a)[4][Nq], int &code,
+                                            int64_t &g_off)
+{
+  constexpr int Q2 = Nq * Nq;
+  code = __ldg(&fc->code); g_off = __ldg(&fc->g_off);
+  const double *Fp = A.fac + __ldg(&fc->fac_off);
+  const int sj = ((code >> 6) == 0) ? 3 : 6;
+#pragma unroll
+  for (int i = 0; i < Nq; i++) {
+    const int q = FIRST_FIXED ? t + Nq * i : i + Nq * t;
+    a[0][i] = __ldg(Fp + q); a[1][i] = __ldg(Fp + Q2 + q); a[2][i] = __ldg(Fp + 2 * Q2 + q);
+    a[3][i] = __ldg(Fp + sj * Q2 + q);
   }
 }
 
@@ -249,48 +324,46 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
 {
   using L = V3<N, Nq>;
   constexpr int TPE = L::TPE, EPW = L::EPW, Q2 = L::Q2, Q3 = L::Q3, N2 = L::N2, N3 = L::N3;
-  constexpr int PSN = L::PSN, PS = L::PS, ESN = L::ESN, EST = L::EST, SS = L::SS;
+  constexpr int EST = L::EST, SS = L::SS, FS = L::FS;
   extern __shared__ __align__(128) unsigned char smraw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint64_t *bar = reinterpret_cast<uint64_t *>(smraw) + warp;
-  double *W = reinterpret_cast<double *>(smraw + 128) + (size_t)warp * L::PERWARP;
-  double *UB = W, *TBa = UB + L::UBS, *TBb = TBa + L::TBS, *HT = TBb + L::TBS, *FA = HT + L::HTS, *NS = FA + L::FAS;
+  double *W = reinterpret_cast<double *>(smraw) + (size_t)warp * L::PERWARP;
+  double *NS = W, *BX = NS + L::NSS, *BY = BX + L::BUF, *BZ = BY + L::BUF, *HT = BZ + L::BUF, *FA = HT + L::HTS;
+  uint64_t *bar = reinterpret_cast<uint64_t *>(FA + L::FAS);
   const int le = lane / TPE, t = lane % TPE;
   const int slot0 = (blockIdx.x * L::WPB + warp) * EPW;
   const int slot = slot0 + le;
   const bool act = le < EPW && slot < A.n_list;
-  const int e = act ? A.elem_list[slot] : 0;
-  const int64_t noff = act ? A.node_off[e] : -1;
+  const v3_slot *sl = A.slots + (act ? slot : 0);
+  const int64_t noff = act ? __ldg(&sl->node_off) : -1;
   const double *B = c_v3.B, *Dq = c_v3.Dq;
+#define TI(a, b, c) L::ti(a, b, c, le)
 
   if (lane == 0) { mbar_init(bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
   __syncwarp();
 
-  /* ---- neighbour staging: round r covers faces [4r, 4r + nf), nf = 4 (r=0) or 2 (r=1) ---- */
-  int tk_fp = 0, tk_tc = 0, tk_mode = 0;   /* my task of the current round */
-  auto issue_round = [&](int r) {
-    const int nf = r == 0 ? 4 : 2;
-    const int tle = lane / nf, tf = 4 * r + lane % nf;
+  /* ---- neighbour staging: round r covers faces 2r, 2r+1 of every element of the batch ---- */
+  int tk_code = 0;
+  auto issue_round = [&](int r) -> uint32_t {
+    const int tle = lane >> 1, tf = 2 * r + (lane & 1);
     const int tslot = slot0 + tle;
-    tk_mode = 0;
+    tk_code = 0;
     uint32_t bytes = 0;
     const double *su = nullptr, *sa = nullptr;
-    if (tle < EPW && tslot < A.n_list) {
-      const int rec = A.frec[6 * tslot + tf];
-      const int nr = A.nrec[6 * tslot + tf];
-      const d4b_hm_t *h = A.hm + rec;
-      const int nb = h->nbr;
-      if (nb >= 0) {
-        tk_fp = h->f_p; tk_tc = h->tcode; tk_mode = nr >= 0 ? 1 : 2;
-        su = (nb < A.n_local) ? A.u + A.node_off[nb] : A.u_ghost + (A.node_off[nb] - A.local_nodes);
-        sa = nr >= 0 ? A.fac + A.hm[nr].fac_off : A.fac + h->fac_off + 3 * Q2;
+    if (lane < 2 * EPW && tslot < A.n_list) {
+      const v3_face *fc = &A.slots[tslot].f[tf];
+      tk_code = __ldg(&fc->code);
+      if (tk_code >> 6) {
+        const int64_t nu = __ldg(&fc->nbr_u);
+        su = nu >= 0 ? A.u + nu : A.u_ghost + (-nu - 1);
+        sa = A.fac + __ldg(&fc->nbr_a);
         if (L::BULK && ((((uintptr_t)su) | ((uintptr_t)sa)) & 15) == 0) bytes = (N3 + 3 * Q2) * 8;
       }
     }
     const uint32_t total = __reduce_add_sync(FULL, bytes);
     if (lane == 0 && total) mbar_expect_tx(bar, total);
     __syncwarp();
-    if (tk_mode) {
+    if (tk_code >> 6) {
       double *dst = NS + lane * SS;
       if (bytes) {
         bulk_g2s(dst, su, N3 * 8, bar);
@@ -302,125 +375,126 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
     }
     return total;
   };
-  auto run_round = [&](int r, uint32_t total, uint32_t parity) {
-    if (total) mbar_wait(bar, parity);
-    __syncwarp();
-    const int nf = r == 0 ? 4 : 2;
-    if (tk_mode) {
-      const int tle = lane / nf, tf = 4 * r + lane % nf;
-      v3_nbr_trace<N, Nq>(NS + lane * SS, tk_fp, tk_tc, tk_mode, FA + (tle * 6 + tf) * 2 * Q2);
-    }
-    __syncwarp();
-  };
   uint32_t npar = 0;
-  uint32_t tot0 = issue_round(0);
+  uint32_t tot = issue_round(0);
 
-  /* ---- own u -> UB (padded), coalesced ---- */
+  /* L2 prefetch of this element's metric block and own face factors (consumed much later) */
+  if (act) {
+    const char *g = reinterpret_cast<const char *>(A.G + 6 * __ldg(&sl->quad_off));
+    for (int o = t * 128; o < 6 * Q3 * 8; o += TPE * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
+    for (int f = t; f < 6; f += TPE) {
+      const char *p = reinterpret_cast<const char *>(A.fac + __ldg(&sl->f[f].fac_off));
+      for (int o = 0; o < 7 * Q2 * 8; o += 128)
+        if (o < 3 * Q2 * 8 || o + 128 > 6 * Q2 * 8) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+    }
+  }
+
+  /* ---- own u -> BX, coalesced ---- */
 #pragma unroll 1
   for (int ee = 0; ee < EPW; ee++) {
     const int64_t base = __shfl_sync(FULL, noff, ee * TPE);
     if (base >= 0)
-      for (int n = lane; n < N3; n += 32) UB[ee * ESN + n + n / N2] = __ldg(A.u + base + n);
+      for (int n = lane; n < N3; n += 32)
+        BX[ee * EST + L::ti(n % N, (n / N) % N, n / N2, ee)] = __ldg(A.u + base + n);
   }
   __syncwarp();
-  double *UBe = UB + le * ESN, *TAe = TBa + le * EST, *TBe = TBb + le * EST;
+  double *Xe = BX + le * EST, *Ye = BY + le * EST, *Ze = BZ + le * EST;
 
-  /* P1 (layout C, nodal): thread k = t < N holds u(:,:,k); B_r, B_s in registers -> v(a,b,k) */
+  /* P1 (layout C, nodal): thread k = t < N holds u(:,:,k); B_r, B_s in registers -> v(a,b,k) -> BY */
   if (act && t < N) {
     double X[N2], V1[Nq * N], V[Q2];
 #pragma unroll
     for (int j = 0; j < N; j++)
 #pragma unroll
-      for (int i = 0; i < N; i++) X[i + N * j] = UBe[i + N * j + PSN * t];
+      for (int i = 0; i < N; i++) X[i + N * j] = Xe[TI(i, j, t)];
     cx<N, Nq, N, false>(B, X, V1); cy<N, Nq, Nq, false>(B, V1, V);
 #pragma unroll
     for (int b = 0; b < Nq; b++)
 #pragma unroll
-      for (int a = 0; a < Nq; a++) TAe[a + Nq * b + PS * t] = V[a + Nq * b];
+      for (int a = 0; a < Nq; a++) Ye[TI(a, b, t)] = V[a + Nq * b];
   }
   __syncwarp();
-  /* A0 (layout A): thread a = t holds (b,c); B_t -> ut; write ut (T2) and g_t (T3) */
-  {
+  /* A0 (layout A): thread a = t holds (b,c); B_t -> ut; write ut -> BX (T2) and g_t -> BZ (T3) */
+  if (act) {
     double V[Nq * N], ut[Q2], gt[Q2];
-    if (act) {
 #pragma unroll
-      for (int k = 0; k < N; k++)
+    for (int k = 0; k < N; k++)
 #pragma unroll
-        for (int b = 0; b < Nq; b++) V[b + Nq * k] = TAe[t + Nq * b + PS * k];
-      cy<N, Nq, Nq, false>(B, V, ut);
-      cy<Nq, Nq, Nq, false>(Dq, ut, gt);
-    }
-    __syncwarp();
-    if (act) {
+      for (int b = 0; b < Nq; b++) V[b + Nq * k] = Ye[TI(t, b, k)];
+    cy<N, Nq, Nq, false>(B, V, ut);
+    cy<Nq, Nq, Nq, false>(Dq, ut, gt);
 #pragma unroll
-      for (int c = 0; c < Nq; c++)
+    for (int c = 0; c < Nq; c++)
 #pragma unroll
-        for (int b = 0; b < Nq; b++) {
-          TAe[t + Nq * b + PS * c] = ut[b + Nq * c];
-          TBe[t + Nq * b + PS * c] = gt[b + Nq * c];
-        }
-    }
+      for (int b = 0; b < Nq; b++) { Xe[TI(t, b, c)] = ut[b + Nq * c]; Ze[TI(t, b, c)] = gt[b + Nq * c]; }
   }
   __syncwarp();
-  run_round(0, tot0, npar); if (tot0) npar ^= 1;
-  uint32_t tot1 = issue_round(1);
 
-  /* C0 (layout C): thread c = t holds (a,b): g_r -> T4; faces 0,1 (normal r) */
-  {
-    double uC[Q2], gtC[Q2], gr[Q2], rC[Q2];
-    if (act) {
-#pragma unroll
-      for (int b = 0; b < Nq; b++)
-#pragma unroll
-        for (int a = 0; a < Nq; a++) { uC[a + Nq * b] = TAe[a + Nq * b + PS * t]; gtC[a + Nq * b] = TBe[a + Nq * b + PS * t]; }
-      cx<Nq, Nq, Nq, false>(Dq, uC, gr);
+  /* ---- three rounds of neighbour traces; faces 0,1 are consumed (layout C) right after round 0 ---- */
+#pragma unroll 1
+  for (int r = 0; r < 3; r++) {
+    if (tot) { mbar_wait(bar, npar); npar ^= 1; }
+    __syncwarp();
+    if (tk_code >> 6) {
+      double *S = NS + lane * SS;
+      double *out = r == 0 ? S : FA + ((lane >> 1) * 4 + 2 * (r - 1) + (lane & 1)) * FS;
+      v3_nbr_trace<N, Nq>(S, (tk_code >> 3) & 7, tk_code & 7, tk_code >> 6, out);
     }
     __syncwarp();
-    if (act) {
+    if (r == 0) {
+      /* C0 (layout C): thread c = t holds (a,b): faces 0,1 (normal r), then g_r -> BY (T4) */
+      if (act) {
+        double uC[Q2], rC[Q2];
 #pragma unroll
-      for (int b = 0; b < Nq; b++)
+        for (int b = 0; b < Nq; b++)
 #pragma unroll
-        for (int a = 0; a < Nq; a++) { TBe[a + Nq * b + PS * t] = gr[a + Nq * b]; rC[a + Nq * b] = 0.; }
+          for (int a = 0; a < Nq; a++) { uC[a + Nq * b] = Xe[TI(a, b, t)]; rC[a + Nq * b] = 0.; }
 #pragma unroll
-      for (int s = 0; s < 2; s++) {
-        double ut[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+        for (int s = 0; s < 2; s++) {
+          double fa[4][Nq]; int code; int64_t goff;
+          v3_load_fac<Nq, false>(A, &sl->f[s], t, fa, code, goff);
+          double ut[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
 #pragma unroll
-        for (int b = 0; b < Nq; b++) {
-          double s0 = 0., s1 = 0., s2 = 0.;
+          for (int b = 0; b < Nq; b++) {
+            double s0 = 0., s1 = 0., s2 = 0.;
 #pragma unroll
-          for (int a = 0; a < Nq; a++) {
-            s0 = fma(c_v3.e[s][a], uC[a + Nq * b], s0); s1 = fma(c_v3.ed[s][a], uC[a + Nq * b], s1);
-            s2 = fma(c_v3.e[s][a], gtC[a + Nq * b], s2);
+            for (int a = 0; a < Nq; a++) {
+              s0 = fma(c_v3.e[s][a], uC[a + Nq * b], s0); s1 = fma(c_v3.ed[s][a], uC[a + Nq * b], s1);
+              s2 = fma(c_v3.e[s][a], Ze[TI(a, b, t)], s2);
+            }
+            ut[b] = s0; dr[b] = s1; dt[b] = s2;
           }
-          ut[b] = s0; dr[b] = s1; dt[b] = s2;
+#pragma unroll
+          for (int b = 0; b < Nq; b++) {
+            double s0 = 0.;
+#pragma unroll
+            for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], ut[m], s0);
+            ds[b] = s0;
+          }
+          v3_flux<Nq, false>(A, code, goff, NS + (2 * le + s) * SS, t, fa, ut, dr, ds, dt, F, Hr, Hs, Ht);
+#pragma unroll
+          for (int b = 0; b < Nq; b++) {
+            double s0 = F[b];
+#pragma unroll
+            for (int m = 0; m < Nq; m++) s0 = fma(Dq[m * Nq + b], Hs[m], s0);
+#pragma unroll
+            for (int a = 0; a < Nq; a++)
+              rC[a + Nq * b] = fma(c_v3.e[s][a], s0, fma(c_v3.ed[s][a], Hr[b], rC[a + Nq * b]));
+            HT[(le * 2 + s) * Q2 + b + Nq * t] = Ht[b];
+          }
         }
+        /* g_r = Dq_r ut -> BY (T4);  rC parked in BZ over g_t (same thread, same addresses) */
+        double gr[Q2];
+        cx<Nq, Nq, Nq, false>(Dq, uC, gr);
 #pragma unroll
-        for (int b = 0; b < Nq; b++) {
-          double s0 = 0.;
+        for (int b = 0; b < Nq; b++)
 #pragma unroll
-          for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], ut[m], s0);
-          ds[b] = s0;
-        }
-        const d4b_hm_t *h = A.hm + A.frec[6 * slot + s];
-        v3_flux<Nq, false>(A, h, FA + (le * 6 + s) * 2 * Q2, t, ut, dr, ds, dt, F, Hr, Hs, Ht);
-#pragma unroll
-        for (int b = 0; b < Nq; b++) {
-          double s0 = F[b];
-#pragma unroll
-          for (int m = 0; m < Nq; m++) s0 = fma(Dq[m * Nq + b], Hs[m], s0);
-#pragma unroll
-          for (int a = 0; a < Nq; a++)
-            rC[a + Nq * b] = fma(c_v3.e[s][a], s0, fma(c_v3.ed[s][a], Hr[b], rC[a + Nq * b]));
-          HT[(le * 2 + s) * Q2 + b + Nq * t] = Ht[b];
-        }
+          for (int a = 0; a < Nq; a++) { Ye[TI(a, b, t)] = gr[a + Nq * b]; Ze[TI(a, b, t)] = rC[a + Nq * b]; }
       }
-      /* park rC (layout C) in UB: read back by the same thread in C1 */
-#pragma unroll
-      for (int i = 0; i < Q2; i++) UB[le * L::UBS / EPW + i * TPE + t] = rC[i];
+      __syncwarp();
     }
+    if (r < 2) tot = issue_round(r + 1);
   }
-  __syncwarp();
-  run_round(1, tot1, npar); if (tot1) npar ^= 1;
 
   /* A1 (layout A): thread a = t holds (b,c): faces 2..5, metric, s/t transposed derivatives */
   {
@@ -431,11 +505,13 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
       for (int c = 0; c < Nq; c++)
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
-          ut[b + Nq * c] = TAe[t + Nq * b + PS * c]; gr[b + Nq * c] = TBe[t + Nq * b + PS * c];
+          ut[b + Nq * c] = Xe[TI(t, b, c)]; gr[b + Nq * c] = Ye[TI(t, b, c)];
           rA[b + Nq * c] = 0.; hrF[b + Nq * c] = 0.;
         }
 #pragma unroll
       for (int s = 0; s < 2; s++) { /* faces 2,3: normal s (index b); my points (a=t, c) */
+        double fa[4][Nq]; int code; int64_t goff;
+        v3_load_fac<Nq, true>(A, &sl->f[2 + s], t, fa, code, goff);
         double tr[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
 #pragma unroll
         for (int c = 0; c < Nq; c++) {
@@ -454,8 +530,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
           for (int m = 0; m < Nq; m++) s0 = fma(Dq[c * Nq + m], tr[m], s0);
           dt[c] = s0;
         }
-        const d4b_hm_t *h = A.hm + A.frec[6 * slot + 2 + s];
-        v3_flux<Nq, true>(A, h, FA + (le * 6 + 2 + s) * 2 * Q2, t, tr, dr, ds, dt, F, Hr, Hs, Ht);
+        v3_flux<Nq, true>(A, code, goff, FA + (le * 4 + s) * FS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
 #pragma unroll
         for (int c = 0; c < Nq; c++) {
           double s0 = F[c];
@@ -470,6 +545,8 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
       }
 #pragma unroll
       for (int s = 0; s < 2; s++) { /* faces 4,5: normal t (index c); my points (a=t, b) */
+        double fa[4][Nq]; int code; int64_t goff;
+        v3_load_fac<Nq, true>(A, &sl->f[4 + s], t, fa, code, goff);
         double tr[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
@@ -488,8 +565,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
           for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], tr[m], s0);
           ds[b] = s0;
         }
-        const d4b_hm_t *h = A.hm + A.frec[6 * slot + 4 + s];
-        v3_flux<Nq, true>(A, h, FA + (le * 6 + 4 + s) * 2 * Q2, t, tr, dr, ds, dt, F, Hr, Hs, Ht);
+        v3_flux<Nq, true>(A, code, goff, FA + (le * 4 + 2 + s) * FS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
           double s0 = F[b];
@@ -502,84 +578,88 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
           }
         }
       }
-      /* metric: h = G g at my points (a=t,b,c); h_t also receives the lift of faces 0,1 */
+      /* metric: h = G g at my points (a=t,b,c), one c-row of G loads in flight at a time;
+       * h_t also receives the lift of faces 0,1 */
       double gs[Q2], gt[Q2];
       cx<Nq, Nq, Nq, false>(Dq, ut, gs); cy<Nq, Nq, Nq, false>(Dq, ut, gt);
-      const double *Ge = A.G + 6 * A.quad_off[e] + t;
+      const double *Ge = A.G + 6 * __ldg(&sl->quad_off) + t;
       const double e0 = c_v3.e[0][t], e1 = c_v3.e[1][t];
       const double *HTe = HT + le * 2 * Q2;
 #pragma unroll
-      for (int c = 0; c < Nq; c++)
+      for (int c = 0; c < Nq; c++) {
+        double Gv[6][Nq];
+#pragma unroll
+        for (int k = 0; k < 6; k++)
+#pragma unroll
+          for (int b = 0; b < Nq; b++) Gv[k][b] = __ldg(Ge + k * Q3 + Nq * (b + Nq * c));
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
-          const int i = b + Nq * c, q = Nq * i;
-          const double G0 = __ldg(Ge + q), G1 = __ldg(Ge + Q3 + q), G2 = __ldg(Ge + 2 * Q3 + q),
-                       G3 = __ldg(Ge + 3 * Q3 + q), G4 = __ldg(Ge + 4 * Q3 + q), G5 = __ldg(Ge + 5 * Q3 + q);
+          const int i = b + Nq * c;
           const double a = gr[i], bb = gs[i], cc = gt[i];
-          gr[i] = G0 * a + G1 * bb + G2 * cc + hrF[i];
-          gs[i] = G1 * a + G3 * bb + G4 * cc;
-          gt[i] = G2 * a + G4 * bb + G5 * cc + e0 * HTe[i] + e1 * HTe[Q2 + i];
+          gr[i] = Gv[0][b] * a + Gv[1][b] * bb + Gv[2][b] * cc + hrF[i];
+          gs[i] = Gv[1][b] * a + Gv[3][b] * bb + Gv[4][b] * cc;
+          gt[i] = Gv[2][b] * a + Gv[4][b] * bb + Gv[5][b] * cc + e0 * HTe[i] + e1 * HTe[Q2 + i];
         }
+      }
       cx_acc<Nq, Nq, Nq, true>(Dq, gs, rA); cy_acc<Nq, Nq, Nq, true>(Dq, gt, rA);
-      /* h_r -> T5 (same addresses this thread read ut from) */
+      /* h_r -> BX (T5; same addresses this thread read ut from) */
 #pragma unroll
       for (int c = 0; c < Nq; c++)
 #pragma unroll
-        for (int b = 0; b < Nq; b++) TAe[t + Nq * b + PS * c] = gr[b + Nq * c];
+        for (int b = 0; b < Nq; b++) Xe[TI(t, b, c)] = gr[b + Nq * c];
     }
     __syncwarp();
-    /* C1 (layout C): rC += Dq_r^T h_r ; rC -> T7 */
+    /* C1 (layout C): rC (parked in BZ) += Dq_r^T h_r ; rC -> BY (T7) */
     if (act) {
       double hr[Q2], rC[Q2];
 #pragma unroll
       for (int b = 0; b < Nq; b++)
 #pragma unroll
-        for (int a = 0; a < Nq; a++) hr[a + Nq * b] = TAe[a + Nq * b + PS * t];
-#pragma unroll
-      for (int i = 0; i < Q2; i++) rC[i] = UB[le * L::UBS / EPW + i * TPE + t];
+        for (int a = 0; a < Nq; a++) { hr[a + Nq * b] = Xe[TI(a, b, t)]; rC[a + Nq * b] = Ze[TI(a, b, t)]; }
       cx_acc<Nq, Nq, Nq, true>(Dq, hr, rC);
 #pragma unroll
       for (int b = 0; b < Nq; b++)
 #pragma unroll
-        for (int a = 0; a < Nq; a++) TBe[a + Nq * b + PS * t] = rC[a + Nq * b];
+        for (int a = 0; a < Nq; a++) Ye[TI(a, b, t)] = rC[a + Nq * b];
     }
     __syncwarp();
-    /* A2 (layout A): rt = rA + rC ; B_t^T, B_s^T in registers -> y(a; j,k) -> T8 */
+    /* A2 (layout A): rt = rA + rC ; B_t^T, B_s^T in registers -> y(a; j,k) -> BX (T8) */
     if (act) {
       double Y1[Nq * N], Y[N2];
 #pragma unroll
       for (int c = 0; c < Nq; c++)
 #pragma unroll
-        for (int b = 0; b < Nq; b++) rA[b + Nq * c] += TBe[t + Nq * b + PS * c];
+        for (int b = 0; b < Nq; b++) rA[b + Nq * c] += Ye[TI(t, b, c)];
       cy<Nq, N, Nq, true>(B, rA, Y1);   /* contract c -> k : Y1[b + Nq k] */
       cx<Nq, N, N, true>(B, Y1, Y);     /* contract b -> j : Y[j + N k]   */
 #pragma unroll
       for (int k = 0; k < N; k++)
 #pragma unroll
-        for (int j = 0; j < N; j++) TAe[t + Nq * j + PS * k] = Y[j + N * k];
+        for (int j = 0; j < N; j++) Xe[TI(t, j, k)] = Y[j + N * k];
     }
   }
   __syncwarp();
-  /* C2 (layout C, nodal): thread k = t < N: B_r^T -> Au(i,j,k) -> UB (padded) */
+  /* C2 (layout C, nodal): thread k = t < N: B_r^T -> Au(i,j,k) -> BZ */
   if (act && t < N) {
     double Yc[Nq * N], O[N2];
 #pragma unroll
     for (int j = 0; j < N; j++)
 #pragma unroll
-      for (int a = 0; a < Nq; a++) Yc[a + Nq * j] = TAe[a + Nq * j + PS * t];
+      for (int a = 0; a < Nq; a++) Yc[a + Nq * j] = Xe[TI(a, j, t)];
     cx<Nq, N, N, true>(B, Yc, O);
 #pragma unroll
     for (int j = 0; j < N; j++)
 #pragma unroll
-      for (int i = 0; i < N; i++) UBe[i + N * j + PSN * t] = O[i + N * j];
+      for (int i = 0; i < N; i++) Ze[TI(i, j, t)] = O[i + N * j];
   }
   __syncwarp();
 #pragma unroll 1
   for (int ee = 0; ee < EPW; ee++) {
     const int64_t base = __shfl_sync(FULL, noff, ee * TPE);
     if (base >= 0)
-      for (int n = lane; n < N3; n += 32) A.Au[base + n] = UB[ee * ESN + n + n / N2];
+      for (int n = lane; n < N3; n += 32) A.Au[base + n] = BZ[ee * EST + L::ti(n % N, (n / N) % N, n / N2, ee)];
   }
+#undef TI
 }
 
 /* ------------------------------------------------------------------ host side */
@@ -632,10 +712,17 @@ static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double
     D4B_CUDA(cudaFuncSetAttribute(d4b_apply_v3_kernel<N, Nq>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM));
     attr = true;
   }
+  if (!b.v3_slots) { /* resolve the per-slot metadata once (tables are immutable after create) */
+    v3_slot *s = nullptr;
+    D4B_CUDA(cudaMalloc((void **)&s, (size_t)b.count * sizeof(v3_slot)));
+    v3_build_slots<<<(b.count + 127) / 128, 128, 0, st>>>(b.count, b.elem_list, b.frec, b.nrec, m->hm, m->node_off,
+                                                        m->quad_off, m->n_local, m->local_nodes, Nq * Nq, s);
+    D4B_CUDA(cudaGetLastError());
+    const_cast<d4b_fast_bucket &>(b).v3_slots = s;
+  }
   v3_args A;
-  A.node_off = m->node_off; A.quad_off = m->quad_off; A.G = m->G; A.hm = m->hm; A.fac = m->fac; A.bc_g = m->bc_g;
-  A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.elem_list = b.elem_list; A.frec = b.frec; A.nrec = b.nrec;
-  A.n_list = b.count; A.n_local = m->n_local; A.local_nodes = m->local_nodes;
+  A.slots = (const v3_slot *)b.v3_slots; A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
+  A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.n_list = b.count;
   const int per = L::EPW * L::WPB;
   d4b_apply_v3_kernel<N, Nq><<<(b.count + per - 1) / per, L::THREADS, L::SMEM, st>>>(A);
   D4B_CUDA(cudaGetLastError());

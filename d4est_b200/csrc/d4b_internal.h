@@ -26,6 +26,7 @@ struct d4b_fast_bucket {
   int N, Nq, count;
   int32_t *elem_list;   /* device: element ids                                          */
   int32_t *frec;        /* device: [count][6] half-mortar record index of face f        */
+  void *v3_slots;       /* device: resolved per-slot metadata of d4b_apply_v3.cu (lazy)        */
   int32_t *nrec;        /* device: [count][6] record of the NEIGHBOUR for the same face (its a- is my
                            -a+), -1 boundary, -2 none (ghost / not mirrored: use my own a+)   */
 };
