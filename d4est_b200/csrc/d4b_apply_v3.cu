@@ -275,7 +275,7 @@ __device__ __forceinline__ void v3_nbr_trace(const double *S, int f_p, int tc, i
  * in: own trace ut and reference gradient (dr,ds,dt);  NB: neighbour trace pair (u+ at +0, q+ at +Q2).
  * out: F (tested with v), Hr/Hs/Ht (tested with dv/dr_l). */
 template <int Nq, bool FIRST_FIXED>
-__device__ __forceinline__ void v3_flux(const v3_args &A, int code, int64_t g_off, const double *NB, int t,
+__device__ __forceinline__ void v3_flux(const v3_args &A, int code, const v3_face *fc, const double *NB, int t,
                                         const double (&a)[4][Nq], const double (&ut)[Nq], const double (&dr)[Nq],
                                         const double (&ds)[Nq], const double (&dt)[Nq], double (&F)[Nq],
                                         double (&Hr)[Nq], double (&Hs)[Nq], double (&Ht)[Nq])
@@ -283,6 +283,7 @@ __device__ __forceinline__ void v3_flux(const v3_args &A, int code, int64_t g_of
   constexpr int Q2 = Nq * Nq;
   const bool bnd = (code >> 6) == 0;
   const int tc = code & 7;
+  const int64_t g_off = bnd ? __ldg(&fc->g_off) : -1;
   const double wt = c_v3.w[t];
 #pragma unroll
   for (int i = 0; i < Nq; i++) {
@@ -304,12 +305,10 @@ __device__ __forceinline__ void v3_flux(const v3_args &A, int code, int64_t g_of
 }
 /* the 4 x Nq own-side factors of a face at my points: issued early so the loads overlap the traces */
 template <int Nq, bool FIRST_FIXED>
-__device__ __forceinline__ void v3_load_fac(const v3_args &A, const v3_face *fc, int t, double (&a)[4][Nq], int &code,
-                                            int64_t &g_off)
+__device__ __forceinline__ void v3_load_fac(const v3_args &A, int64_t fac_off, int code, int t, double (&a)[4][Nq])
 {
   constexpr int Q2 = Nq * Nq;
-  code = __ldg(&fc->code); g_off = __ldg(&fc->g_off);
-  const double *Fp = A.fac + __ldg(&fc->fac_off);
+  const double *Fp = A.fac + fac_off;
   const int sj = ((code >> 6) == 0) ? 3 : 6;
 #pragma unroll
   for (int i = 0; i < Nq; i++) {
@@ -331,16 +330,21 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
   double *NS = W, *BX = NS + L::NSS, *BY = BX + L::BUF, *BZ = BY + L::BUF, *HT = BZ + L::BUF, *FA = HT + L::HTS;
   uint64_t *bar = reinterpret_cast<uint64_t *>(FA + L::FAS);
   const int le = lane / TPE, t = lane % TPE;
-  const int slot0 = (blockIdx.x * L::WPB + warp) * EPW;
+  const double *B = c_v3.B, *Dq = c_v3.Dq;
+#define TI(a, b, c) L::ti(a, b, c, le)
+  if (lane == 0) { mbar_init(bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  __syncwarp();
+  uint32_t npar = 0;
+  /* persistent: every warp walks its own batches of EPW elements; warps never synchronise with
+   * each other, so their load phases drift apart and overlap with the other warps' arithmetic */
+  const int nbatch = (A.n_list + EPW - 1) / EPW;
+#pragma unroll 1
+  for (int batch = blockIdx.x * L::WPB + warp; batch < nbatch; batch += gridDim.x * L::WPB) {
+  const int slot0 = batch * EPW;
   const int slot = slot0 + le;
   const bool act = le < EPW && slot < A.n_list;
   const v3_slot *sl = A.slots + (act ? slot : 0);
   const int64_t noff = act ? __ldg(&sl->node_off) : -1;
-  const double *B = c_v3.B, *Dq = c_v3.Dq;
-#define TI(a, b, c) L::ti(a, b, c, le)
-
-  if (lane == 0) { mbar_init(bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-  __syncwarp();
 
   /* ---- neighbour staging: round r covers faces 2r, 2r+1 of every element of the batch ---- */
   int tk_code = 0;
@@ -375,7 +379,6 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
     }
     return total;
   };
-  uint32_t npar = 0;
   uint32_t tot = issue_round(0);
 
   /* L2 prefetch of this element's metric block and own face factors (consumed much later) */
@@ -389,13 +392,26 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
     }
   }
 
-  /* ---- own u -> BX, coalesced ---- */
-#pragma unroll 1
-  for (int ee = 0; ee < EPW; ee++) {
-    const int64_t base = __shfl_sync(FULL, noff, ee * TPE);
-    if (base >= 0)
-      for (int n = lane; n < N3; n += 32)
-        BX[ee * EST + L::ti(n % N, (n / N) % N, n / N2, ee)] = __ldg(A.u + base + n);
+  /* ---- own u -> BX, coalesced; all loads of the batch in flight before the first store ---- */
+  {
+    constexpr int PL = (N3 + 31) / 32;
+    double uv[EPW][PL];
+#pragma unroll
+    for (int ee = 0; ee < EPW; ee++) {
+      const int64_t base = __shfl_sync(FULL, noff, ee * TPE);
+#pragma unroll
+      for (int m = 0; m < PL; m++) {
+        const int n = lane + 32 * m;
+        uv[ee][m] = (base >= 0 && n < N3) ? __ldg(A.u + base + n) : 0.;
+      }
+    }
+#pragma unroll
+    for (int ee = 0; ee < EPW; ee++)
+#pragma unroll
+      for (int m = 0; m < PL; m++) {
+        const int n = lane + 32 * m;
+        if (n < N3) BX[ee * EST + L::ti(n % N, (n / N) % N, n / N2, ee)] = uv[ee][m];
+      }
   }
   __syncwarp();
   double *Xe = BX + le * EST, *Ye = BY + le * EST, *Ze = BZ + le * EST;
@@ -445,14 +461,17 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
       /* C0 (layout C): thread c = t holds (a,b): faces 0,1 (normal r), then g_r -> BY (T4) */
       if (act) {
         double uC[Q2], rC[Q2];
+        int64_t foff[2]; int fcode[2];
+#pragma unroll
+        for (int s = 0; s < 2; s++) { foff[s] = __ldg(&sl->f[s].fac_off); fcode[s] = __ldg(&sl->f[s].code); }
 #pragma unroll
         for (int b = 0; b < Nq; b++)
 #pragma unroll
           for (int a = 0; a < Nq; a++) { uC[a + Nq * b] = Xe[TI(a, b, t)]; rC[a + Nq * b] = 0.; }
 #pragma unroll
         for (int s = 0; s < 2; s++) {
-          double fa[4][Nq]; int code; int64_t goff;
-          v3_load_fac<Nq, false>(A, &sl->f[s], t, fa, code, goff);
+          double fa[4][Nq]; const int code = fcode[s];
+          v3_load_fac<Nq, false>(A, foff[s], code, t, fa);
           double ut[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
 #pragma unroll
           for (int b = 0; b < Nq; b++) {
@@ -471,7 +490,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
             for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], ut[m], s0);
             ds[b] = s0;
           }
-          v3_flux<Nq, false>(A, code, goff, NS + (2 * le + s) * SS, t, fa, ut, dr, ds, dt, F, Hr, Hs, Ht);
+          v3_flux<Nq, false>(A, code, &sl->f[s], NS + (2 * le + s) * SS, t, fa, ut, dr, ds, dt, F, Hr, Hs, Ht);
 #pragma unroll
           for (int b = 0; b < Nq; b++) {
             double s0 = F[b];
@@ -501,6 +520,9 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
     double rA[Q2];
     if (act) {
       double ut[Q2], gr[Q2], hrF[Q2];
+      int64_t foff[4]; int fcode[4];
+#pragma unroll
+      for (int f = 0; f < 4; f++) { foff[f] = __ldg(&sl->f[2 + f].fac_off); fcode[f] = __ldg(&sl->f[2 + f].code); }
 #pragma unroll
       for (int c = 0; c < Nq; c++)
 #pragma unroll
@@ -510,8 +532,8 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
         }
 #pragma unroll
       for (int s = 0; s < 2; s++) { /* faces 2,3: normal s (index b); my points (a=t, c) */
-        double fa[4][Nq]; int code; int64_t goff;
-        v3_load_fac<Nq, true>(A, &sl->f[2 + s], t, fa, code, goff);
+        double fa[4][Nq]; const int code = fcode[s];
+        v3_load_fac<Nq, true>(A, foff[s], code, t, fa);
         double tr[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
 #pragma unroll
         for (int c = 0; c < Nq; c++) {
@@ -530,7 +552,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
           for (int m = 0; m < Nq; m++) s0 = fma(Dq[c * Nq + m], tr[m], s0);
           dt[c] = s0;
         }
-        v3_flux<Nq, true>(A, code, goff, FA + (le * 4 + s) * FS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
+        v3_flux<Nq, true>(A, code, &sl->f[2 + s], FA + (le * 4 + s) * FS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
 #pragma unroll
         for (int c = 0; c < Nq; c++) {
           double s0 = F[c];
@@ -545,8 +567,8 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
       }
 #pragma unroll
       for (int s = 0; s < 2; s++) { /* faces 4,5: normal t (index c); my points (a=t, b) */
-        double fa[4][Nq]; int code; int64_t goff;
-        v3_load_fac<Nq, true>(A, &sl->f[4 + s], t, fa, code, goff);
+        double fa[4][Nq]; const int code = fcode[2 + s];
+        v3_load_fac<Nq, true>(A, foff[2 + s], code, t, fa);
         double tr[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
@@ -565,7 +587,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
           for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], tr[m], s0);
           ds[b] = s0;
         }
-        v3_flux<Nq, true>(A, code, goff, FA + (le * 4 + 2 + s) * FS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
+        v3_flux<Nq, true>(A, code, &sl->f[4 + s], FA + (le * 4 + 2 + s) * FS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
           double s0 = F[b];
@@ -659,6 +681,8 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
     if (base >= 0)
       for (int n = lane; n < N3; n += 32) A.Au[base + n] = BZ[ee * EST + L::ti(n % N, (n / N) % N, n / N2, ee)];
   }
+  __syncwarp();
+  } /* batch loop */
 #undef TI
 }
 
@@ -723,8 +747,16 @@ static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double
   v3_args A;
   A.slots = (const v3_slot *)b.v3_slots; A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
   A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.n_list = b.count;
+  static int n_sm = 0;
+  if (!n_sm) { int dev = 0; D4B_CUDA(cudaGetDevice(&dev)); D4B_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
   const int per = L::EPW * L::WPB;
-  d4b_apply_v3_kernel<N, Nq><<<(b.count + per - 1) / per, L::THREADS, L::SMEM, st>>>(A);
+  int grid = (b.count + per - 1) / per;
+  /* one batch per warp by default: the warps of a CTA then run in phase and share the instruction
+   * cache (the kernel is ~100 KB of SASS); D4B_V3_PERSISTENT=1 caps the grid at one CTA per SM */
+  static int persist = -1;
+  if (persist < 0) persist = getenv("D4B_V3_PERSISTENT") != nullptr;
+  if (persist && grid > n_sm) grid = n_sm;
+  d4b_apply_v3_kernel<N, Nq><<<grid, L::THREADS, L::SMEM, st>>>(A);
   D4B_CUDA(cudaGetLastError());
   d4b_count_launch(1);
   return D4B_OK;
