@@ -171,15 +171,17 @@ template <int N, int Nq> struct V3 {
   static constexpr int EST = SWZ ? 64 : ((Nq * PS + 3) / 4) * 4; /* element stride of X/Y/Z buffers */
   static constexpr int BUF = EPW * EST;
   static constexpr int HTS = EPW * 2 * Q2;
-  static constexpr int FS = 2 * Q2 + 1;              /* stride of one neighbour-trace pair in FA   */
-  static constexpr int FAS = ((EPW * 4 * FS + 3) / 4) * 4;   /* faces 2..5                         */
   static constexpr int TASKD = N3 + 3 * Q2;          /* doubles staged per neighbour face          */
   static constexpr int SS = TASKD + (((TASKD / 2) % 2 == 0) ? 2 : 0) + (TASKD % 2); /* even, SS/2 odd */
   static constexpr int NSLOT = 2 * EPW;              /* one round = faces 2r, 2r+1 of all elements */
   static constexpr int NSS = NSLOT * SS;
-  static constexpr int PERWARP = 3 * BUF + HTS + FAS + NSS + 2; /* doubles; +2: mbarrier          */
-  static constexpr int WPB_MAX = (227 * 1024) / (PERWARP * 8);
-  static constexpr int WPB = WPB_MAX >= 6 ? 6 : (WPB_MAX >= 1 ? WPB_MAX : 1);
+  static constexpr int BARPAD = SS > TASKD ? 0 : 2;  /* the mbarrier sits in the pad of slot 0     */
+  static constexpr int PERWARP = NSS + 3 * BUF + HTS + BARPAD; /* doubles                          */
+  static constexpr int SM_BYTES = 233472, CTA_RESERVED = 1024;
+  static constexpr bool TWO = 2 * (4 * PERWARP * 8 + CTA_RESERVED) <= SM_BYTES;   /* 2 CTAs x 4 warps */
+  static constexpr int WPB_MAX = (SM_BYTES - CTA_RESERVED) / (PERWARP * 8);
+  static constexpr int WPB = TWO ? 4 : (WPB_MAX >= 6 ? 6 : (WPB_MAX >= 1 ? WPB_MAX : 1));
+  static constexpr int CTAS = TWO ? 2 : 1;
   static constexpr int THREADS = 32 * WPB;
   static constexpr size_t SMEM = (size_t)WPB * PERWARP * 8;
   static constexpr bool BULK = (N3 % 2 == 0) && (Q2 % 2 == 0);
@@ -319,16 +321,16 @@ __device__ __forceinline__ void v3_load_fac(const v3_args &A, int64_t fac_off, i
 }
 
 template <int N, int Nq>
-__global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(const v3_args A)
+__global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply_v3_kernel(const v3_args A)
 {
   using L = V3<N, Nq>;
   constexpr int TPE = L::TPE, EPW = L::EPW, Q2 = L::Q2, Q3 = L::Q3, N2 = L::N2, N3 = L::N3;
-  constexpr int EST = L::EST, SS = L::SS, FS = L::FS;
+  constexpr int EST = L::EST, SS = L::SS;
   extern __shared__ __align__(128) unsigned char smraw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *W = reinterpret_cast<double *>(smraw) + (size_t)warp * L::PERWARP;
-  double *NS = W, *BX = NS + L::NSS, *BY = BX + L::BUF, *BZ = BY + L::BUF, *HT = BZ + L::BUF, *FA = HT + L::HTS;
-  uint64_t *bar = reinterpret_cast<uint64_t *>(FA + L::FAS);
+  double *NS = W, *BX = NS + L::NSS, *BY = BX + L::BUF, *BZ = BY + L::BUF, *HT = BZ + L::BUF;
+  uint64_t *bar = reinterpret_cast<uint64_t *>(L::BARPAD ? HT + L::HTS : NS + L::TASKD);
   const int le = lane / TPE, t = lane % TPE;
   const double *B = c_v3.B, *Dq = c_v3.Dq;
 #define TI(a, b, c) L::ti(a, b, c, le)
@@ -446,15 +448,16 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
   }
   __syncwarp();
 
-  /* ---- three rounds of neighbour traces; faces 0,1 are consumed (layout C) right after round 0 ---- */
+  /* ---- three rounds of neighbour traces, each consumed from its slots right after it is built:
+   *      faces 0,1 in layout C (C0), faces 2,3 in layout A (A1a), faces 4,5 after the loop (A1b) ---- */
+  double Hr23[2][Nq];
 #pragma unroll 1
   for (int r = 0; r < 3; r++) {
     if (tot) { mbar_wait(bar, npar); npar ^= 1; }
     __syncwarp();
     if (tk_code >> 6) {
       double *S = NS + lane * SS;
-      double *out = r == 0 ? S : FA + ((lane >> 1) * 4 + 2 * (r - 1) + (lane & 1)) * FS;
-      v3_nbr_trace<N, Nq>(S, (tk_code >> 3) & 7, tk_code & 7, tk_code >> 6, out);
+      v3_nbr_trace<N, Nq>(S, (tk_code >> 3) & 7, tk_code & 7, tk_code >> 6, S);
     }
     __syncwarp();
     if (r == 0) {
@@ -512,24 +515,20 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
       }
       __syncwarp();
     }
-    if (r < 2) tot = issue_round(r + 1);
-  }
-
-  /* A1 (layout A): thread a = t holds (b,c): faces 2..5, metric, s/t transposed derivatives */
-  {
-    double rA[Q2];
-    if (act) {
-      double ut[Q2], gr[Q2], hrF[Q2];
-      int64_t foff[4]; int fcode[4];
+    if (r == 1) {
+      /* A1a (layout A): thread a = t holds (b,c): faces 2,3; their lift goes straight into the
+       * residual accumulator BZ (which already holds the layout-C part), H_r stays in registers */
+      if (act) {
+        double ut[Q2], gr[Q2], rA[Q2];
+        int64_t foff[2]; int fcode[2];
 #pragma unroll
-      for (int f = 0; f < 4; f++) { foff[f] = __ldg(&sl->f[2 + f].fac_off); fcode[f] = __ldg(&sl->f[2 + f].code); }
+        for (int f = 0; f < 2; f++) { foff[f] = __ldg(&sl->f[2 + f].fac_off); fcode[f] = __ldg(&sl->f[2 + f].code); }
 #pragma unroll
-      for (int c = 0; c < Nq; c++)
+        for (int c = 0; c < Nq; c++)
 #pragma unroll
-        for (int b = 0; b < Nq; b++) {
-          ut[b + Nq * c] = Xe[TI(t, b, c)]; gr[b + Nq * c] = Ye[TI(t, b, c)];
-          rA[b + Nq * c] = 0.; hrF[b + Nq * c] = 0.;
-        }
+          for (int b = 0; b < Nq; b++) {
+            ut[b + Nq * c] = Xe[TI(t, b, c)]; gr[b + Nq * c] = Ye[TI(t, b, c)]; rA[b + Nq * c] = 0.;
+          }
 #pragma unroll
       for (int s = 0; s < 2; s++) { /* faces 2,3: normal s (index b); my points (a=t, c) */
         double fa[4][Nq]; const int code = fcode[s];
@@ -552,19 +551,45 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
           for (int m = 0; m < Nq; m++) s0 = fma(Dq[c * Nq + m], tr[m], s0);
           dt[c] = s0;
         }
-        v3_flux<Nq, true>(A, code, &sl->f[2 + s], FA + (le * 4 + s) * FS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
+        v3_flux<Nq, true>(A, code, &sl->f[2 + s], NS + (2 * le + s) * SS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
 #pragma unroll
         for (int c = 0; c < Nq; c++) {
           double s0 = F[c];
 #pragma unroll
           for (int m = 0; m < Nq; m++) s0 = fma(Dq[m * Nq + c], Ht[m], s0);
+          Hr23[s][c] = Hr[c];
 #pragma unroll
           for (int b = 0; b < Nq; b++) {
             rA[b + Nq * c] = fma(c_v3.e[s][b], s0, fma(c_v3.ed[s][b], Hs[c], rA[b + Nq * c]));
-            hrF[b + Nq * c] = fma(c_v3.e[s][b], Hr[c], hrF[b + Nq * c]);
           }
         }
       }
+#pragma unroll
+        for (int c = 0; c < Nq; c++)
+#pragma unroll
+          for (int b = 0; b < Nq; b++) Ze[TI(t, b, c)] += rA[b + Nq * c];
+      }
+      __syncwarp();
+    }
+    if (r < 2) tot = issue_round(r + 1);
+  }
+
+  /* A1b (layout A): faces 4,5, metric, s/t transposed derivatives */
+  {
+    double rA[Q2];
+    if (act) {
+      double ut[Q2], gr[Q2], hrF[Q2];
+      int64_t foff[4]; int fcode[4];
+#pragma unroll
+      for (int f = 2; f < 4; f++) { foff[f] = __ldg(&sl->f[2 + f].fac_off); fcode[f] = __ldg(&sl->f[2 + f].code); }
+#pragma unroll
+      for (int c = 0; c < Nq; c++)
+#pragma unroll
+        for (int b = 0; b < Nq; b++) {
+          ut[b + Nq * c] = Xe[TI(t, b, c)]; gr[b + Nq * c] = Ye[TI(t, b, c)];
+          rA[b + Nq * c] = 0.;
+          hrF[b + Nq * c] = c_v3.e[0][b] * Hr23[0][c] + c_v3.e[1][b] * Hr23[1][c];
+        }
 #pragma unroll
       for (int s = 0; s < 2; s++) { /* faces 4,5: normal t (index c); my points (a=t, b) */
         double fa[4][Nq]; const int code = fcode[2 + s];
@@ -587,7 +612,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
           for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], tr[m], s0);
           ds[b] = s0;
         }
-        v3_flux<Nq, true>(A, code, &sl->f[4 + s], FA + (le * 4 + 2 + s) * FS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
+        v3_flux<Nq, true>(A, code, &sl->f[4 + s], NS + (2 * le + s) * SS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
           double s0 = F[b];
@@ -624,14 +649,14 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
         }
       }
       cx_acc<Nq, Nq, Nq, true>(Dq, gs, rA); cy_acc<Nq, Nq, Nq, true>(Dq, gt, rA);
-      /* h_r -> BX (T5; same addresses this thread read ut from) */
+      /* h_r -> BX (T5; same addresses this thread read ut from); residual part -> accumulator BZ */
 #pragma unroll
       for (int c = 0; c < Nq; c++)
 #pragma unroll
-        for (int b = 0; b < Nq; b++) Xe[TI(t, b, c)] = gr[b + Nq * c];
+        for (int b = 0; b < Nq; b++) { Xe[TI(t, b, c)] = gr[b + Nq * c]; Ze[TI(t, b, c)] += rA[b + Nq * c]; }
     }
     __syncwarp();
-    /* C1 (layout C): rC (parked in BZ) += Dq_r^T h_r ; rC -> BY (T7) */
+    /* C1 (layout C): residual accumulator (BZ) + Dq_r^T h_r -> BY (T7) */
     if (act) {
       double hr[Q2], rC[Q2];
 #pragma unroll
@@ -651,7 +676,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, 1) d4b_apply_v3_kernel(con
 #pragma unroll
       for (int c = 0; c < Nq; c++)
 #pragma unroll
-        for (int b = 0; b < Nq; b++) rA[b + Nq * c] += Ye[TI(t, b, c)];
+        for (int b = 0; b < Nq; b++) rA[b + Nq * c] = Ye[TI(t, b, c)];
       cy<Nq, N, Nq, true>(B, rA, Y1);   /* contract c -> k : Y1[b + Nq k] */
       cx<Nq, N, N, true>(B, Y1, Y);     /* contract b -> j : Y[j + N k]   */
 #pragma unroll
