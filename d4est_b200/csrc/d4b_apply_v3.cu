@@ -164,6 +164,15 @@ struct v3_args {
   const double *u, *u_ghost; double *Au; int n_list;
 };
 
+/* read-only 8-byte load that the compiler may not sink towards its use: a group of these, issued
+ * back to back, keeps a whole row of independent loads in flight */
+__device__ __forceinline__ double ldg_pin(const double *p)
+{
+  double v;
+  asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+
 template <int N, int Nq> struct V3 {
   static constexpr int TPE = Nq, EPW = 32 / Nq, Q2 = Nq * Nq, Q3 = Q2 * Nq, N2 = N * N, N3 = N2 * N;
   static constexpr bool SWZ = (N == 4 && Nq == 4);   /* XOR-swizzled 64-double element blocks      */
@@ -315,8 +324,8 @@ __device__ __forceinline__ void v3_load_fac(const v3_args &A, int64_t fac_off, i
 #pragma unroll
   for (int i = 0; i < Nq; i++) {
     const int q = FIRST_FIXED ? t + Nq * i : i + Nq * t;
-    a[0][i] = __ldg(Fp + q); a[1][i] = __ldg(Fp + Q2 + q); a[2][i] = __ldg(Fp + 2 * Q2 + q);
-    a[3][i] = __ldg(Fp + sj * Q2 + q);
+    a[0][i] = ldg_pin(Fp + q); a[1][i] = ldg_pin(Fp + Q2 + q); a[2][i] = ldg_pin(Fp + 2 * Q2 + q);
+    a[3][i] = ldg_pin(Fp + sj * Q2 + q);
   }
 }
 
@@ -627,6 +636,10 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
       }
       /* metric: h = G g at my points (a=t,b,c), one c-row of G loads in flight at a time;
        * h_t also receives the lift of faces 0,1 */
+#pragma unroll
+      for (int c = 0; c < Nq; c++)
+#pragma unroll
+        for (int b = 0; b < Nq; b++) { Ze[TI(t, b, c)] += rA[b + Nq * c]; rA[b + Nq * c] = 0.; }
       double gs[Q2], gt[Q2];
       cx<Nq, Nq, Nq, false>(Dq, ut, gs); cy<Nq, Nq, Nq, false>(Dq, ut, gt);
       const double *Ge = A.G + 6 * __ldg(&sl->quad_off) + t;
@@ -638,7 +651,8 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
 #pragma unroll
         for (int k = 0; k < 6; k++)
 #pragma unroll
-          for (int b = 0; b < Nq; b++) Gv[k][b] = __ldg(Ge + k * Q3 + Nq * (b + Nq * c));
+          for (int b = 0; b < Nq; b++) Gv[k][b] = ldg_pin(Ge + k * Q3 + Nq * (b + Nq * c));
+        asm volatile("" ::: "memory");
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
           const int i = b + Nq * c;
