@@ -53,33 +53,59 @@ def reference_arm(args, rank):
     print(json.dumps(line))
 
 
-class ClockSampler(threading.Thread):
+class ClockSampler:
+    """Streams `nvidia-smi -lms 20` for one GPU while the timed region runs (clocks + throttle reasons)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, dev):
-        super().__init__(daemon=True)
-        self.dev, self.stop_flag, self.rows = dev, False, []
+        self.rows, self.proc, self.thr = [], None, None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(dev), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+        except Exception:
+            self.proc = None
 
-    def run(self):
-        while not self.stop_flag:
-            try:
-                o = subprocess.run(["nvidia-smi", "-i", str(self.dev), f"--query-gpu={self.Q}",
-                                    "--format=csv,noheader,nounits"], stdout=subprocess.PIPE, text=True, timeout=5).stdout
-                self.rows.append([c.strip() for c in o.strip().split(",")])
-            except Exception:
-                pass
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [c.strip() for c in ln.strip().split(",")]))
+
+    def start(self):
+        if self.thr:
+            self.thr.start()
+            time.sleep(0.3)  # let the first samples arrive before the timed region starts
+
+    def mark(self):
+        return time.perf_counter()
+
+    def summary(self, t0=None, t1=None):
+        if self.proc:
             time.sleep(0.05)
-
-    def summary(self):
-        self.stop_flag = True
-        self.join(timeout=6)
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=3)
+            except Exception:
+                self.proc.kill()
+        rows = [r for (ts, r) in self.rows if (t0 is None or ts >= t0) and (t1 is None or ts <= t1 + 0.05)]
+        if not rows:
+            rows = [r for (_, r) in self.rows]
+        sm = sorted(int(r[0]) for r in rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in rows if len(r) > 1 and r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
+        reasons = sorted({names[i] for r in rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(sm)}
+
+
+def ncu_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the apply kernel on this workload, from the
+    committed `ncu --set full` capture (profiles/ncu_traffic.json); None when no capture exists for it."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(workload, {}).get("dram_bytes")
+    except Exception:
+        return None
 
 
 def cpu_baseline(args):
@@ -104,7 +130,7 @@ def cpu_baseline(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--n", type=int, default=100, help="brick elements per direction (per GPU)")
@@ -147,17 +173,20 @@ def main():
         lvl.apply_dev(u.data_ptr(), Au.data_ptr(), st)
     barrier()
     sampler = ClockSampler(local); sampler.start()
+    barrier()
     n0 = L.d4b_kernel_launches()
+    t_begin = sampler.mark()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     ev[0].record()
     for i in range(args.steps):
         lvl.apply_dev(u.data_ptr(), Au.data_ptr(), st)
         ev[i + 1].record()
     barrier()
+    t_end = sampler.mark()
     launches = int(L.d4b_kernel_launches() - n0)
     total_ms = ev[0].elapsed_time(ev[-1])
     per = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps))
-    clocks = sampler.summary()
+    clocks = sampler.summary(t_begin, t_end)
     tmax = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -200,7 +229,7 @@ def main():
                            "l2": f"inputs larger than L2 (resident tables {lvl.resident_bytes / 1e9:.2f} GB, vectors {2 * ndof * 8 / 1e9:.2f} GB)",
                            "parallelism": f"{world} x independent brick (halo exchange not in the timed path yet)" if world > 1 else "1 GPU"},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak,
-                             "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                             "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(workload_name(args.n, args.deg)),
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                              "algorithmic_bytes_per_launch": alg, "bytes_per_dof": alg / ndof, "kernel_ms": kern_ms},
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": ndof * 8, "d2h_bytes_per_step": ndof * 8,
