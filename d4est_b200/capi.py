@@ -50,6 +50,7 @@ SYMBOLS = {
     "d4b_mesh_create": (C.c_int, [C.POINTER(MeshDesc), C.POINTER(_P)]),
     "d4b_mesh_destroy": (None, [_P]),
     "d4b_brick_create": (C.c_int, [C.POINTER(BrickParams), C.POINTER(_P)]),
+    "d4b_brick_create_slab": (C.c_int, [C.POINTER(BrickParams), C.c_int, C.c_int, C.POINTER(_P)]),
     "d4b_mesh_local_nodes": (C.c_int64, [_P]),
     "d4b_mesh_ghost_nodes": (C.c_int64, [_P]),
     "d4b_mesh_bytes": (C.c_int64, [_P]),
@@ -160,12 +161,29 @@ class Multigrid:
 _lib = None
 
 
+def _preload_nccl():
+    """libd4est_b200.so needs libnccl.so.2.  When the process also hosts torch (tests, bench), both must bind
+    to ONE NCCL: load the copy bundled with torch's wheels first (nvidia/nccl/lib) so that a later `import torch`
+    does not meet the older system library; without that wheel the system libnccl is used."""
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia")
+        for base in (spec.submodule_search_locations if spec else []):
+            cand = os.path.join(base, "nccl", "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                C.CDLL(cand, mode=C.RTLD_GLOBAL)
+                return
+    except Exception:
+        pass
+
+
 def lib():
     global _lib
     if _lib is None:
         if not os.path.exists(LIB_PATH):
             raise D4BError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
                            "(there is no CPU fallback)")
+        _preload_nccl()
         _lib = C.CDLL(LIB_PATH)
         for name, (res, args) in SYMBOLS.items():
             fn = getattr(_lib, name)
@@ -220,14 +238,16 @@ class MeshLevel:
         self.n_local = nl
 
     @classmethod
-    def brick(cls, n, deg=3, degq=None, quad_type=0, prefactor=2.0, box=(0., 1., 0., 1., 0., 1.), face_h=0.0):
-        """Synthetic uniform brick generated on the device (d4b_brick_create)."""
+    def brick(cls, n, deg=3, degq=None, quad_type=0, prefactor=2.0, box=(0., 1., 0., 1., 0., 1.), face_h=0.0,
+              rank=0, nranks=1):
+        """Synthetic uniform brick generated on the device (d4b_brick_create); with nranks > 1 the z-slab
+        `rank` of the brick nx x ny x (nz*nranks), with ghost planes and halo lists (d4b_brick_create_slab)."""
         nx, ny, nz = (n, n, n) if np.isscalar(n) else n
         p = BrickParams(nx, ny, nz, deg, deg if degq is None else degq, quad_type, *box, prefactor, face_h)
         self = cls(None)
-        check(lib().d4b_brick_create(C.byref(p), C.byref(self.handle)))
+        check(lib().d4b_brick_create_slab(C.byref(p), rank, nranks, C.byref(self.handle)))
         self.local_nodes = int(lib().d4b_mesh_local_nodes(self.handle))
-        self.ghost_nodes = 0
+        self.ghost_nodes = int(lib().d4b_mesh_ghost_nodes(self.handle))
         self.n_local = nx * ny * nz
         return self
 

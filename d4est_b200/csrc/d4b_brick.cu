@@ -11,6 +11,7 @@
 
 struct brick_dev {
   int nx, ny, nz, Nq, n_elem;
+  int ghost_lo, ghost_hi;   /* first ghost id of the plane below / above the slab, or -1 (physical boundary) */
   double hx, hy, hz, sig;   /* element widths, sigma = prefactor p^2 / h */
   const int32_t *emap;      /* grid cell -> element id */
   const int32_t *ecoord;    /* element -> packed ix | iy<<10 | iz<<20 */
@@ -39,8 +40,12 @@ __global__ void brick_fill_faces(brick_dev B, d4b_hm_t *__restrict__ hm, double 
   int jx = ix + (d == 0 ? (s ? 1 : -1) : 0), jy = iy + (d == 1 ? (s ? 1 : -1) : 0),
       jz = iz + (d == 2 ? (s ? 1 : -1) : 0);
   bool bnd = jx < 0 || jy < 0 || jz < 0 || jx >= B.nx || jy >= B.ny || jz >= B.nz;
+  int ghost = -1; /* neighbour in the slab of the rank below / above: ghost planes are ordered ix + nx iy */
+  if (jz < 0 && B.ghost_lo >= 0) ghost = B.ghost_lo + jx + B.nx * jy;
+  if (jz >= B.nz && B.ghost_hi >= 0) ghost = B.ghost_hi + jx + B.nx * jy;
+  if (ghost >= 0) bnd = false;
   d4b_hm_t h;
-  h.nbr = bnd ? -1 : B.emap[jx + B.nx * (jy + B.ny * jz)];
+  h.nbr = bnd ? -1 : (ghost >= 0 ? B.n_elem + ghost : B.emap[jx + B.nx * (jy + B.ny * jz)]);
   h.f_m = (int8_t)f; h.f_p = (int8_t)(bnd ? -1 : (f ^ 1)); h.tcode = 1; h.child_m = -1; h.child_p = -1;
   h.degq = (int8_t)(B.Nq - 1); h.face_slot = (int8_t)f; h.pad = 0; h.pad0 = 0;
   h.fac_off = t * 7 * n2; h.g_off = -1; h.pad2 = 0;
@@ -66,7 +71,7 @@ __global__ void brick_fill_nrec(int n6, const d4b_hm_t *__restrict__ hm, int32_t
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n6) return;
   int nb = hm[t].nbr;
-  nrec[t] = nb < 0 ? -1 : 6 * nb + ((t % 6) ^ 1);
+  nrec[t] = nb < 0 ? -1 : (6 * nb >= n6 ? -2 /* ghost: no record here, fold with my own a+ */ : 6 * nb + ((t % 6) ^ 1));
 }
 
 static inline uint64_t morton3(uint32_t x, uint32_t y, uint32_t z)
@@ -78,7 +83,17 @@ static inline uint64_t morton3(uint32_t x, uint32_t y, uint32_t z)
   return k;
 }
 
-extern "C" int d4b_brick_create(const d4b_brick_params_t *p, d4b_mesh_t **out)
+static int brick_create_slab(const d4b_brick_params_t *p, int rank, int nranks, d4b_mesh_t **out);
+extern "C" int d4b_brick_create(const d4b_brick_params_t *p, d4b_mesh_t **out) { return brick_create_slab(p, 0, 1, out); }
+/* z-slab `rank` of the brick nx x ny x (nz * nranks) over the same box: one slab per rank (= GPU), ghost
+ * planes towards rank-1 / rank+1, mirror lists for d4b_halo_exchange (weak scaling: nz per rank is fixed) */
+extern "C" int d4b_brick_create_slab(const d4b_brick_params_t *p, int rank, int nranks, d4b_mesh_t **out)
+{
+  if (nranks < 1 || rank < 0 || rank >= nranks) { d4b_set_error("d4b_brick_create_slab: bad rank"); return D4B_EINVAL; }
+  return brick_create_slab(p, rank, nranks, out);
+}
+
+static int brick_create_slab(const d4b_brick_params_t *p, int rank, int nranks, d4b_mesh_t **out)
 {
   *out = nullptr;
   if (!p || p->nx < 1 || p->ny < 1 || p->nz < 1 || p->nx > 1023 || p->ny > 1023 || p->nz > 1023 ||
@@ -93,23 +108,41 @@ extern "C" int d4b_brick_create(const d4b_brick_params_t *p, d4b_mesh_t **out)
   for (int iz = 0; iz < p->nz; iz++) for (int iy = 0; iy < p->ny; iy++) for (int ix = 0; ix < p->nx; ix++)
     keys[k++] = { morton3(ix, iy, iz), ix | (iy << 10) | (iz << 20) };
   std::sort(keys.begin(), keys.end());
-  std::vector<int32_t> ecoord((size_t)ne), emap((size_t)ne), deg((size_t)ne, p->deg), degq((size_t)ne, p->degq), hb((size_t)ne + 1);
-  std::vector<int64_t> node_off((size_t)ne + 1), quad_off((size_t)ne + 1);
+  const bool has_lo = rank > 0, has_hi = rank < nranks - 1;
+  const int64_t plane = (int64_t)p->nx * p->ny, ng = plane * ((has_lo ? 1 : 0) + (has_hi ? 1 : 0));
+  std::vector<int32_t> ecoord((size_t)ne), emap((size_t)ne), deg((size_t)(ne + ng), p->deg), degq((size_t)ne, p->degq), hb((size_t)ne + 1);
+  std::vector<int64_t> node_off((size_t)(ne + ng) + 1), quad_off((size_t)ne + 1);
   for (int64_t e = 0; e < ne; e++) {
     int c = keys[e].second; ecoord[e] = c;
     emap[(c & 1023) + p->nx * (((c >> 10) & 1023) + (int64_t)p->ny * ((c >> 20) & 1023))] = (int32_t)e;
   }
-  for (int64_t e = 0; e <= ne; e++) { node_off[e] = e * N * N * N; quad_off[e] = e * Nq * Nq * Nq; hb[e] = (int32_t)(6 * e); }
+  for (int64_t e = 0; e <= ne; e++) { quad_off[e] = e * Nq * Nq * Nq; hb[e] = (int32_t)(6 * e); }
+  for (int64_t e = 0; e <= ne + ng; e++) node_off[e] = e * N * N * N;
+  /* halo lists: peers in rank order (below, above); mirrors = my bottom / top plane in ix + nx iy order */
+  std::vector<int32_t> peer_rank, send_begin(1, 0), send_elem, recv_begin(1, 0);
+  for (int side = 0; side < 2; side++) {
+    if (!(side == 0 ? has_lo : has_hi)) continue;
+    peer_rank.push_back(side == 0 ? rank - 1 : rank + 1);
+    const int iz = side == 0 ? 0 : p->nz - 1;
+    for (int iy = 0; iy < p->ny; iy++) for (int ix = 0; ix < p->nx; ix++)
+      send_elem.push_back(emap[ix + p->nx * (iy + (int64_t)p->ny * iz)]);
+    send_begin.push_back((int32_t)send_elem.size());
+    recv_begin.push_back((int32_t)(recv_begin.back() + plane));
+  }
   d4b_mesh_desc_t D; memset(&D, 0, sizeof D);
   int32_t zero1[1] = {0};
+  D.n_ghost = (int32_t)ng; D.n_peers = (int32_t)peer_rank.size(); D.peer_rank = peer_rank.data();
+  D.send_elem = send_elem.data();
   D.n_local = (int32_t)ne; D.quad_type = p->quad_type; D.deg = deg.data(); D.node_off = node_off.data();
   D.degq = degq.data(); D.quad_off = quad_off.data(); D.hm_begin = hb.data();
-  D.n_fac = 6 * ne * 7 * Nq * Nq; D.send_begin = zero1; D.recv_begin = zero1;
+  D.n_fac = 6 * ne * 7 * Nq * Nq; D.send_begin = send_begin.data(); D.recv_begin = recv_begin.data();
+  (void)zero1;
   d4b_mesh *m = nullptr;
   int rc = d4b_mesh_create(&D, &m);
   if (rc != D4B_OK) return rc;
   brick_dev B; B.nx = p->nx; B.ny = p->ny; B.nz = p->nz; B.Nq = Nq; B.n_elem = (int)ne;
-  B.hx = (p->x1 - p->x0) / p->nx; B.hy = (p->y1 - p->y0) / p->ny; B.hz = (p->z1 - p->z0) / p->nz;
+  B.hx = (p->x1 - p->x0) / p->nx; B.hy = (p->y1 - p->y0) / p->ny; B.hz = (p->z1 - p->z0) / ((double)p->nz * nranks);
+  B.ghost_lo = has_lo ? 0 : -1; B.ghost_hi = has_hi ? (int)(has_lo ? plane : 0) : -1;
   double h = p->face_h > 0 ? p->face_h : 1.0 / p->nx;
   B.sig = p->penalty_prefactor * (double)p->deg * (double)p->deg / h;
   int32_t *d_emap = nullptr, *d_ecoord = nullptr; double *d_w = nullptr;
@@ -132,7 +165,7 @@ extern "C" int d4b_brick_create(const d4b_brick_params_t *p, d4b_mesh_t **out)
   cudaFree(d_emap); cudaFree(d_ecoord); cudaFree(d_w);
   /* algorithmic bytes: u + Au + 6-component metric + 7 doubles per UNIQUE interior
    * mortar point (each appears in two half-mortars) + 4 per boundary point */
-  int64_t nb = 2 * ((int64_t)p->nx * p->ny + (int64_t)p->ny * p->nz + (int64_t)p->nx * p->nz);
+  int64_t nb = 2 * ((int64_t)p->ny * p->nz + (int64_t)p->nx * p->nz) + plane * ((has_lo ? 0 : 1) + (has_hi ? 0 : 1));
   int64_t ni = (6 * ne - nb) / 2;
   m->alg_bytes = ne * (16 * (int64_t)N * N * N + 48 * (int64_t)Nq * Nq * Nq) + (ni * 56 + nb * 32) * Nq * Nq;
   m->max_degq = p->degq;

@@ -126,6 +126,10 @@ typedef struct d4b_brick_params {
   double face_h;            /* h in the penalty; <= 0 means 1/nx (= dq/ROOT_LEN)        */
 } d4b_brick_params_t;
 int d4b_brick_create(const d4b_brick_params_t *p, d4b_mesh_t **out);
+/* One z-slab per rank of the brick nx x ny x (nz*nranks) over the same box (the p4est partition of a
+ * brick forest cut along z): ghost planes towards rank-1 / rank+1 and the mirror lists that
+ * d4b_halo_exchange uses (d4est_ghost_t / d4est_ghost_data_exchange, Mesh/d4est_ghost_data.c:143). */
+int d4b_brick_create_slab(const d4b_brick_params_t *p, int rank, int nranks, d4b_mesh_t **out);
 
 /* ---- operator apply: replaces d4est_laplacian_with_opt_apply_aij
  *      (dGMath/d4est_laplacian_with_opt.c:289) and its twin d4est_laplacian_apply_aij
