@@ -730,9 +730,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
 
 bool d4b_v3_supported(int N, int Nq)
 {
-  static int off = -1;
-  if (off < 0) off = getenv("D4B_NO_V3") != nullptr;
-  if (off) return false;
+  if (getenv("D4B_NO_V3") != nullptr) return false;   /* test switch: route the bucket to the line-task kernel */
 #define X(a, b) if (N == a && Nq == b) return true;
   V3_PAIRS(X)
 #undef X

@@ -60,3 +60,29 @@ def test_repeatable_bitwise(golden_dir):
     a, b = lvl.apply_host(fx["u"]), lvl.apply_host(fx["u"])
     assert np.array_equal(a, b)  # no atomics anywhere on the path
     assert d4est_b200.lib().d4b_kernel_launches() > 0
+
+
+@pytest.mark.parametrize("name", ["brick_p3_l3_poly", "cubed_sphere_p3_uniform"])
+def test_register_blocked_kernel_equals_line_kernel_and_generic(name, ref_fixture_dir):
+    """The three element kernels (v3 register-blocked, v2 line tasks, generic) are interchangeable on regular
+    elements: same Au to round-off on a brick with inhomogeneous Dirichlet data and on the curved cubed sphere with
+    uniform p=3 (all 832 elements regular, five inter-tree orientation codes)."""
+    p = os.path.join(ref_fixture_dir, name + ".fix")
+    if not os.path.exists(p):
+        pytest.skip("reference fixture not built")
+    fx = fixture.load(p)
+    out = {}
+    for key, env in (("v3", {}), ("v2", {"D4B_NO_V3": "1"}), ("generic", {"D4B_NO_FAST": "1"})):
+        for k, v in env.items():
+            os.environ[k] = v
+        try:
+            n0 = d4est_b200.lib().d4b_kernel_launches()
+            lvl = d4est_b200.MeshLevel(fx)
+            out[key] = lvl.apply_host(fx["u"])
+            lvl.close()
+        finally:
+            for k in env:
+                del os.environ[k]
+    for key in out:
+        assert rel(out[key], fx["Au_ref_with_opt"]) < TOL, key
+    assert rel(out["v3"], out["v2"]) < 1e-13 and rel(out["v3"], out["generic"]) < 1e-13
