@@ -23,6 +23,21 @@ struct d4b_gen_args {
   int qt, NX, NQX, MX;
 };
 
+/* idx / d for 0 <= idx < 2^15, 1 <= d <= 64, with inv = (2^20 + d - 1) / d computed once per stage */
+__device__ __forceinline__ int fdiv_small(int idx, unsigned inv) { return (int)(((unsigned long long)(unsigned)idx * inv) >> 20); }
+
+template <int COLS>
+__device__ __forceinline__ double dot_fixed(const double *__restrict__ Mr, int cs, const double *inb, int stride)
+{
+  double m[COLS], x[COLS];
+#pragma unroll
+  for (int k = 0; k < COLS; k++) { m[k] = __ldg(&Mr[k * cs]); x[k] = inb[k * stride]; }   /* all loads in flight */
+  double s = 0.;
+#pragma unroll
+  for (int k = 0; k < COLS; k++) s = fma(m[k], x[k], s);
+  return s;
+}
+
 /* out = (M applied along axis ax) in;  M(r,k) = M[r*rs + k*cs]; in dims (n0,n1,n2), n[ax]=cols */
 __device__ __forceinline__ void contract(const double *__restrict__ M, int rs, int cs, int rows, int cols,
                                          const double *in, double *out, int n0, int n1, int n2, int ax,
@@ -31,12 +46,26 @@ __device__ __forceinline__ void contract(const double *__restrict__ M, int rs, i
   const int o0 = ax == 0 ? rows : n0, o1 = ax == 1 ? rows : n1, o2 = ax == 2 ? rows : n2;
   const int total = o0 * o1 * o2;
   const int stride = ax == 0 ? 1 : (ax == 1 ? n0 : n0 * n1);
+  const unsigned inv0 = ((1u << 20) + o0 - 1) / o0, inv1 = ((1u << 20) + o1 - 1) / o1;
   for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-    int i0 = idx % o0, i1 = (idx / o0) % o1, i2 = idx / (o0 * o1);
+    const int q0 = fdiv_small(idx, inv0), i0 = idx - q0 * o0;
+    const int i2 = fdiv_small(q0, inv1), i1 = q0 - i2 * o1;
     int r = ax == 0 ? i0 : (ax == 1 ? i1 : i2);
     int base = (ax == 0 ? 0 : i0) + n0 * ((ax == 1 ? 0 : i1) + n1 * (ax == 2 ? 0 : i2));
-    double s = 0.;
-    for (int k = 0; k < cols; k++) s = fma(__ldg(&M[r * rs + k * cs]), in[base + k * stride], s);
+    const double *Mr = M + r * rs, *inb = in + base;
+    double s;
+    switch (cols) { /* 1-D sizes are 2..16: fixed trip counts keep every load of the dot product in flight */
+      case 2: s = dot_fixed<2>(Mr, cs, inb, stride); break;
+      case 3: s = dot_fixed<3>(Mr, cs, inb, stride); break;
+      case 4: s = dot_fixed<4>(Mr, cs, inb, stride); break;
+      case 5: s = dot_fixed<5>(Mr, cs, inb, stride); break;
+      case 6: s = dot_fixed<6>(Mr, cs, inb, stride); break;
+      case 7: s = dot_fixed<7>(Mr, cs, inb, stride); break;
+      case 8: s = dot_fixed<8>(Mr, cs, inb, stride); break;
+      default:
+        s = 0.;
+        for (int k = 0; k < cols; k++) s = fma(__ldg(&Mr[k * cs]), inb[k * stride], s);
+    }
     out[idx] = accumulate ? out[idx] + s : s;
   }
   __syncthreads();
