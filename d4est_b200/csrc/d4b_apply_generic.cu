@@ -250,7 +250,7 @@ int d4b_launch_generic(const d4b_mesh *m, const double *u, double *Au, const int
   A.qt = m->quad_type; A.NX = m->max_deg_ext + 1; A.NQX = m->max_degq + 1;
   A.MX = A.NX > A.NQX ? A.NX : A.NQX;
   if (A.n_list == 0) return D4B_OK;
-  d4b_apply_generic_kernel<<<A.n_list, 256, m->generic_smem, st>>>(A);
+  d4b_apply_generic_kernel<<<A.n_list, 128, m->generic_smem, st>>>(A);
   D4B_CUDA(cudaGetLastError());
   d4b_count_launch(1);
   return D4B_OK;
