@@ -161,7 +161,7 @@ __global__ void v3_build_slots(int n, const int32_t *__restrict__ elem_list, con
 
 struct v3_args {
   const v3_slot *slots; const double *G; const double *fac; const double *bc_g;
-  const double *u, *u_ghost; double *Au; int n_list;
+  const double *u, *u_ghost; double *Au; int n_list; /* one past the last slot */ int slot_begin;
 };
 
 /* read-only 8-byte load that the compiler may not sink towards its use: a group of these, issued
@@ -348,10 +348,10 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
   uint32_t npar = 0;
   /* persistent: every warp walks its own batches of EPW elements; warps never synchronise with
    * each other, so their load phases drift apart and overlap with the other warps' arithmetic */
-  const int nbatch = (A.n_list + EPW - 1) / EPW;
+  const int nbatch = (A.n_list - A.slot_begin + EPW - 1) / EPW;
 #pragma unroll 1
   for (int batch = blockIdx.x * L::WPB + warp; batch < nbatch; batch += gridDim.x * L::WPB) {
-  const int slot0 = batch * EPW;
+  const int slot0 = A.slot_begin + batch * EPW;
   const int slot = slot0 + le;
   const bool act = le < EPW && slot < A.n_list;
   const v3_slot *sl = A.slots + (act ? slot : 0);
@@ -765,7 +765,8 @@ static int v3_upload_tab(int qt, int N, int Nq, cudaStream_t st)
 }
 
 template <int N, int Nq>
-static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st)
+static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st,
+                       int slot_begin, int slot_end)
 {
   using L = V3<N, Nq>;
   static bool attr = false;
@@ -783,11 +784,12 @@ static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double
   }
   v3_args A;
   A.slots = (const v3_slot *)b.v3_slots; A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
-  A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.n_list = b.count;
+  A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.n_list = slot_end; A.slot_begin = slot_begin;
   static int n_sm = 0;
   if (!n_sm) { int dev = 0; D4B_CUDA(cudaGetDevice(&dev)); D4B_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
   const int per = L::EPW * L::WPB;
-  int grid = (b.count + per - 1) / per;
+  int grid = (slot_end - slot_begin + per - 1) / per;
+  if (grid <= 0) return D4B_OK;
   /* one batch per warp by default: the warps of a CTA then run in phase and share the instruction
    * cache (the kernel is ~100 KB of SASS); D4B_V3_PERSISTENT=1 caps the grid at one CTA per SM */
   static int persist = -1;
@@ -799,12 +801,24 @@ static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double
   return D4B_OK;
 }
 
-int d4b_launch_v3(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st)
+int d4b_launch_v3_range(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st,
+                        int slot_begin, int slot_end)
 {
   int rc = v3_upload_tab(m->quad_type, b.N, b.Nq, st);
   if (rc != D4B_OK) return rc;
-#define X(a, c) if (b.N == a && b.Nq == c) return v3_launch_t<a, c>(m, b, u, Au, st);
+#define X(a, c) if (b.N == a && b.Nq == c) return v3_launch_t<a, c>(m, b, u, Au, st, slot_begin, slot_end);
   V3_PAIRS(X)
 #undef X
   d4b_set_error("d4b_launch_v3: unsupported (N,Nq)"); return D4B_EINVAL;
+}
+
+int d4b_launch_v3(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st)
+{ return d4b_launch_v3_range(m, b, u, Au, st, 0, b.count); }
+
+int d4b_v3_elems_per_cta(int N, int Nq)
+{
+#define X(a, c) if (N == a && Nq == c) return V3<a, c>::EPW * V3<a, c>::WPB;
+  V3_PAIRS(X)
+#undef X
+  return 32;
 }
