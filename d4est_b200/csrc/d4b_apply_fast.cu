@@ -402,12 +402,21 @@ bool d4b_fast_supported(int N, int Nq)
 
 static int upload_tab(int qt, int N, int Nq, cudaStream_t st)
 {
-  static int cur_qt = -1, cur_N = -1, cur_Nq = -1;
-  static fast_tab *h = nullptr;
-  if (cur_qt == qt && cur_N == N && cur_Nq == Nq) return D4B_OK;
-  if (!h) D4B_CUDA(cudaMallocHost((void **)&h, 4 * sizeof(fast_tab))); /* small ring: async copies stay valid */
-  static int ring = 0;
-  fast_tab *t = h + (ring++ & 3);
+  /* one pinned, immutable host copy per (quadrature, N, Nq): an enqueued asynchronous copy to constant
+   * memory may execute long after this call returns, so its source must never be rewritten */
+  static int cur_key = -1;
+  static cudaStream_t cur_st = nullptr;   /* a table enqueued on another stream is not ordered before this launch */
+  static fast_tab *cache[2 * 16 * 16] = {nullptr};
+  const int key = (qt * 16 + N) * 16 + Nq;
+  if (cur_key == key && cur_st == st) return D4B_OK;
+  cur_st = st;
+  if (cache[key]) {
+    D4B_CUDA(cudaMemcpyToSymbolAsync(c_ft, cache[key], sizeof(fast_tab), 0, cudaMemcpyHostToDevice, st));
+    cur_key = key;
+    return D4B_OK;
+  }
+  fast_tab *t = nullptr;
+  D4B_CUDA(cudaMallocHost((void **)&t, sizeof(fast_tab)));
   memset(t, 0, sizeof *t);
   double I[D4B_OPS_MAXN * D4B_OPS_MAXN], Dm[D4B_OPS_MAXN * D4B_OPS_MAXN], x[D4B_OPS_MAXN], w[D4B_OPS_MAXN];
   d4b_ops_interp(N - 1, Nq - 1, qt, -1, I); d4b_ops_diff(N - 1, Dm); d4b_ops_quad(Nq - 1, qt, x, w);
@@ -421,8 +430,9 @@ static int upload_tab(int qt, int N, int Nq, cudaStream_t st)
     }
   }
   for (int i = 0; i < N * N; i++) t->D[i] = Dm[i];
+  cache[key] = t;
   D4B_CUDA(cudaMemcpyToSymbolAsync(c_ft, t, sizeof(fast_tab), 0, cudaMemcpyHostToDevice, st));
-  cur_qt = qt; cur_N = N; cur_Nq = Nq;
+  cur_key = key;
   return D4B_OK;
 }
 

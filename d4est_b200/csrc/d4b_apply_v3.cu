@@ -739,12 +739,21 @@ bool d4b_v3_supported(int N, int Nq)
 
 static int v3_upload_tab(int qt, int N, int Nq, cudaStream_t st)
 {
-  static int cur_qt = -1, cur_N = -1, cur_Nq = -1;
-  static v3_tab *h = nullptr;
-  static int ring = 0;
-  if (cur_qt == qt && cur_N == N && cur_Nq == Nq) return D4B_OK;
-  if (!h) D4B_CUDA(cudaMallocHost((void **)&h, 4 * sizeof(v3_tab)));
-  v3_tab *t = h + (ring++ & 3);
+  /* one pinned, immutable host copy per (quadrature, N, Nq): the asynchronous copy to constant memory may
+   * execute long after this call returns, so the source of an enqueued copy must never be rewritten */
+  static int cur_key = -1;
+  static cudaStream_t cur_st = nullptr;   /* a table enqueued on another stream is not ordered before this launch */
+  static v3_tab *cache[2 * 16 * 16] = {nullptr};
+  const int key = (qt * 16 + N) * 16 + Nq;
+  if (cur_key == key && cur_st == st) return D4B_OK;
+  cur_st = st;
+  if (cache[key]) {
+    D4B_CUDA(cudaMemcpyToSymbolAsync(c_v3, cache[key], sizeof(v3_tab), 0, cudaMemcpyHostToDevice, st));
+    cur_key = key;
+    return D4B_OK;
+  }
+  v3_tab *t = nullptr;
+  D4B_CUDA(cudaMallocHost((void **)&t, sizeof(v3_tab)));
   memset(t, 0, sizeof *t);
   double I[D4B_OPS_MAXN * D4B_OPS_MAXN], Dm[D4B_OPS_MAXN * D4B_OPS_MAXN], Dqm[D4B_OPS_MAXN * D4B_OPS_MAXN];
   double x[D4B_OPS_MAXN], w[D4B_OPS_MAXN], e0[D4B_OPS_MAXN], e1[D4B_OPS_MAXN];
@@ -759,8 +768,9 @@ static int v3_upload_tab(int qt, int N, int Nq, cudaStream_t st)
     for (int a = 0; a < Nq; a++) { s0 += e0[a] * Dqm[a * Nq + m]; s1 += e1[a] * Dqm[a * Nq + m]; }
     t->ed[0][m] = s0; t->ed[1][m] = s1;
   }
+  cache[key] = t;
   D4B_CUDA(cudaMemcpyToSymbolAsync(c_v3, t, sizeof(v3_tab), 0, cudaMemcpyHostToDevice, st));
-  cur_qt = qt; cur_N = N; cur_Nq = Nq;
+  cur_key = key;
   return D4B_OK;
 }
 

@@ -86,3 +86,16 @@ def test_register_blocked_kernel_equals_line_kernel_and_generic(name, ref_fixtur
     for key in out:
         assert rel(out[key], fx["Au_ref_with_opt"]) < TOL, key
     assert rel(out["v3"], out["v2"]) < 1e-13 and rel(out["v3"], out["generic"]) < 1e-13
+
+
+def test_back_to_back_device_applies_on_a_multi_bucket_mesh(golden_dir):
+    """Many asynchronous applies in a row on a mesh with several degree buckets (each launch re-points the
+    constant-memory tables): the last result equals the synchronous host-path result bit for bit."""
+    from d4est_b200.capi import DevVec
+    fx = fixture.load(os.path.join(golden_dir, "cubed_sphere_hp1.fix"))
+    lvl = d4est_b200.MeshLevel(fx)
+    ref = lvl.apply_host(fx["u"])
+    U, V = DevVec(lvl.local_nodes, fx["u"]), DevVec(lvl.local_nodes)
+    for _ in range(60):
+        lvl.apply_dev(U.ptr.value, V.ptr.value, 0)
+    assert np.array_equal(V.get(), ref)
