@@ -190,7 +190,7 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
   free(m->send_node_begin_h); free(m->recv_node_begin_h);
   if (m->stream) cudaStreamDestroy(m->stream);
-  if (m->copy_stream) { cudaStreamDestroy(m->copy_stream); for (int k = 0; k < 8; k++) cudaEventDestroy(m->ev_chunk[k]); }
+  if (m->copy_stream) { cudaStreamDestroy(m->copy_stream); cudaStreamDestroy(m->in_stream); for (int k = 0; k < 16; k++) { cudaEventDestroy(m->ev_out[k]); cudaEventDestroy(m->ev_in[k]); } }
   free(m);
 }
 
@@ -222,35 +222,53 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
     D4B_CUDA(cudaMalloc((void **)&m->u_stage, nb ? nb : 8));
     D4B_CUDA(cudaMalloc((void **)&m->Au_stage, nb ? nb : 8));
   }
-  D4B_CUDA(cudaMemcpyAsync(m->u_stage, u_host, nb, cudaMemcpyHostToDevice, m->stream));
-  /* One degree bucket that covers the whole level in element order (uniform mesh) and a range-capable kernel:
-   * the apply runs as NCH element ranges and the device->host copy of each finished range overlaps the kernel
-   * of the next one (Au of a range is complete when its kernel is: every element writes only its own nodes). */
-  if (m->n_fast == 1 && m->n_generic == 0 && m->fast[0].count == m->n_local && m->fast[0].nrec &&
+  /* One degree bucket that covers the whole level in element order (uniform mesh, no rank boundary) and a
+   * range-capable kernel: the apply runs as a 3-stream pipeline over equal element ranges.  u arrives in chunks;
+   * the kernel of range k starts when the last chunk it reads (own elements + face neighbours, computed once per
+   * level) has arrived; the device->host copy of a finished range overlaps the following kernels and, PCIe
+   * being full duplex, the remaining uploads.  Every element writes only its own nodes of Au. */
+  if (m->n_fast == 1 && m->n_generic == 0 && m->fast[0].count == m->n_local && m->fast[0].nrec && m->n_peers == 0 &&
       d4b_v3_supported(m->fast[0].N, m->fast[0].Nq) && m->n_local >= 8192 && !getenv("D4B_NO_PIPELINE")) {
     const d4b_fast_bucket &b = m->fast[0];
-    const int NCH = 8;
+    const int NCH = 16;
+    const int64_t N3 = (int64_t)b.N * b.N * b.N;
+    int rc0;
     if (!m->copy_stream) {
       D4B_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
-      for (int k = 0; k < NCH; k++) D4B_CUDA(cudaEventCreateWithFlags(&m->ev_chunk[k], cudaEventDisableTiming));
+      D4B_CUDA(cudaStreamCreateWithFlags(&m->in_stream, cudaStreamNonBlocking));
+      for (int k = 0; k < NCH; k++) {
+        D4B_CUDA(cudaEventCreateWithFlags(&m->ev_out[k], cudaEventDisableTiming));
+        D4B_CUDA(cudaEventCreateWithFlags(&m->ev_in[k], cudaEventDisableTiming));
+      }
+      const int per = d4b_v3_elems_per_cta(b.N, b.Nq);
+      m->pipe_chunk = ((m->n_local + NCH - 1) / NCH + per - 1) / per * per;
+      m->pipe_ranges = (m->n_local + m->pipe_chunk - 1) / m->pipe_chunk;
+      if ((rc0 = d4b_v3_range_need(m, b, m->pipe_ranges, m->pipe_chunk, m->pipe_need, m->stream)) != D4B_OK) return rc0;
     }
-    int rc0;
-    if (m->n_peers > 0 && d4b_comm_size() > 1 && (rc0 = d4b_halo_exchange(m, m->u_stage, m->stream)) != D4B_OK) return rc0;
-    const int per = d4b_v3_elems_per_cta(b.N, b.Nq);
-    const int64_t N3 = (int64_t)b.N * b.N * b.N;
-    int chunk = ((m->n_local + NCH - 1) / NCH + per - 1) / per * per;
-    for (int k = 0, s0 = 0; s0 < m->n_local; k++, s0 += chunk) {
-      int s1 = s0 + chunk < m->n_local ? s0 + chunk : m->n_local;
+    const int chunk = m->pipe_chunk, nr = m->pipe_ranges;
+    for (int k = 0; k < nr; k++) {
+      int s0 = k * chunk, s1 = s0 + chunk < m->n_local ? s0 + chunk : m->n_local;
+      D4B_CUDA(cudaMemcpyAsync(m->u_stage + s0 * N3, u_host + s0 * N3, (size_t)(s1 - s0) * N3 * sizeof(double),
+                               cudaMemcpyHostToDevice, m->in_stream));
+      D4B_CUDA(cudaEventRecord(m->ev_in[k], m->in_stream));
+    }
+    int waited = -1;
+    for (int k = 0; k < nr; k++) {
+      int s0 = k * chunk, s1 = s0 + chunk < m->n_local ? s0 + chunk : m->n_local;
+      int need = m->pipe_need[k] < k ? k : (m->pipe_need[k] >= nr ? nr - 1 : m->pipe_need[k]);
+      if (need > waited) { D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_in[need], 0)); waited = need; }
       if ((rc0 = d4b_launch_v3_range(m, b, m->u_stage, m->Au_stage, m->stream, s0, s1)) != D4B_OK) return rc0;
-      D4B_CUDA(cudaEventRecord(m->ev_chunk[k], m->stream));
-      D4B_CUDA(cudaStreamWaitEvent(m->copy_stream, m->ev_chunk[k], 0));
+      D4B_CUDA(cudaEventRecord(m->ev_out[k], m->stream));
+      D4B_CUDA(cudaStreamWaitEvent(m->copy_stream, m->ev_out[k], 0));
       D4B_CUDA(cudaMemcpyAsync(Au_host + s0 * N3, m->Au_stage + s0 * N3, (size_t)(s1 - s0) * N3 * sizeof(double),
                                cudaMemcpyDeviceToHost, m->copy_stream));
     }
     D4B_CUDA(cudaStreamSynchronize(m->copy_stream));
     D4B_CUDA(cudaStreamSynchronize(m->stream));
+    D4B_CUDA(cudaStreamSynchronize(m->in_stream));
     return D4B_OK;
   }
+  D4B_CUDA(cudaMemcpyAsync(m->u_stage, u_host, nb, cudaMemcpyHostToDevice, m->stream));
   int rc = d4b_apply_dev(m, m->u_stage, m->Au_stage, m->stream);
   if (rc != D4B_OK) return rc;
   D4B_CUDA(cudaMemcpyAsync(Au_host, m->Au_stage, nb, cudaMemcpyDeviceToHost, m->stream));

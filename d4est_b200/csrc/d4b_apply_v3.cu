@@ -774,6 +774,49 @@ static int v3_upload_tab(int qt, int N, int Nq, cudaStream_t st)
   return D4B_OK;
 }
 
+static int v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStream_t st)
+{
+  if (b.v3_slots) return D4B_OK;   /* resolved once: the tables are immutable after create */
+  v3_slot *s = nullptr;
+  D4B_CUDA(cudaMalloc((void **)&s, (size_t)b.count * sizeof(v3_slot)));
+  v3_build_slots<<<(b.count + 127) / 128, 128, 0, st>>>(b.count, b.elem_list, b.frec, b.nrec, m->hm, m->node_off,
+                                                      m->quad_off, m->n_local, m->local_nodes, b.Nq * b.Nq, s);
+  D4B_CUDA(cudaGetLastError());
+  const_cast<d4b_fast_bucket &>(b).v3_slots = s;
+  return D4B_OK;
+}
+
+/* For the host-buffer pipeline: need[k] = index of the last u chunk that range k of the bucket reads (its own
+ * elements and their local face neighbours), chunks and ranges being the same equal element ranges. */
+__global__ void v3_range_need(const v3_slot *__restrict__ slots, int n, int chunk, int64_t N3, int *__restrict__ need)
+{
+  const int k = blockIdx.x, s0 = k * chunk, s1 = min(n, s0 + chunk);
+  long long mx = 0;
+  for (int s = s0 + threadIdx.x; s < s1; s += blockDim.x) {
+    long long v = slots[s].node_off;
+    for (int f = 0; f < 6; f++) if ((slots[s].f[f].code >> 6) && slots[s].f[f].nbr_u > v) v = slots[s].f[f].nbr_u;
+    mx = max(mx, v);
+  }
+  __shared__ long long red[256];
+  red[threadIdx.x] = mx; __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) { if (threadIdx.x < o) red[threadIdx.x] = max(red[threadIdx.x], red[threadIdx.x + o]); __syncthreads(); }
+  if (threadIdx.x == 0) need[k] = (int)((red[0] / N3) / chunk);
+}
+
+int d4b_v3_range_need(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, int chunk, int *need_host, cudaStream_t st)
+{
+  int rc = v3_prepare_slots(m, b, st);
+  if (rc != D4B_OK) return rc;
+  int *d = nullptr;
+  D4B_CUDA(cudaMalloc((void **)&d, n_ranges * sizeof(int)));
+  v3_range_need<<<n_ranges, 256, 0, st>>>((const v3_slot *)b.v3_slots, b.count, chunk, (int64_t)b.N * b.N * b.N, d);
+  D4B_CUDA(cudaGetLastError());
+  D4B_CUDA(cudaMemcpyAsync(need_host, d, n_ranges * sizeof(int), cudaMemcpyDeviceToHost, st));
+  D4B_CUDA(cudaStreamSynchronize(st));
+  cudaFree(d);
+  return D4B_OK;
+}
+
 template <int N, int Nq>
 static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st,
                        int slot_begin, int slot_end)
@@ -784,14 +827,7 @@ static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double
     D4B_CUDA(cudaFuncSetAttribute(d4b_apply_v3_kernel<N, Nq>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM));
     attr = true;
   }
-  if (!b.v3_slots) { /* resolve the per-slot metadata once (tables are immutable after create) */
-    v3_slot *s = nullptr;
-    D4B_CUDA(cudaMalloc((void **)&s, (size_t)b.count * sizeof(v3_slot)));
-    v3_build_slots<<<(b.count + 127) / 128, 128, 0, st>>>(b.count, b.elem_list, b.frec, b.nrec, m->hm, m->node_off,
-                                                        m->quad_off, m->n_local, m->local_nodes, Nq * Nq, s);
-    D4B_CUDA(cudaGetLastError());
-    const_cast<d4b_fast_bucket &>(b).v3_slots = s;
-  }
+  { int rcs = v3_prepare_slots(m, b, st); if (rcs != D4B_OK) return rcs; }
   v3_args A;
   A.slots = (const v3_slot *)b.v3_slots; A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
   A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.n_list = slot_end; A.slot_begin = slot_begin;

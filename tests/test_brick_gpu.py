@@ -49,3 +49,19 @@ def test_non_power_of_two_brick_is_spd_and_symmetric():
     x, y = rng.standard_normal(lvl.local_nodes), rng.standard_normal(lvl.local_nodes)
     Ax, Ay = lvl.apply_host(x), lvl.apply_host(y)
     assert abs(y @ Ax - x @ Ay) < 1e-11 * abs(y @ Ax) and x @ Ax > 0
+
+
+def test_host_pipeline_equals_plain_host_path():
+    """d4b_apply_host on a uniform level runs as a 3-stream pipeline over element ranges (chunked H2D, kernel per
+    range once the chunks it reads have arrived, D2H per finished range); D4B_NO_PIPELINE=1 is the plain
+    H2D -> kernel -> D2H path.  Same bits."""
+    import os
+    lvl = d4est_b200.MeshLevel.brick((24, 20, 28), deg=3)   # 13 440 elements: above the pipeline threshold
+    u = np.random.default_rng(3).uniform(-1, 1, lvl.local_nodes)
+    a = lvl.apply_host(u)
+    os.environ["D4B_NO_PIPELINE"] = "1"
+    try:
+        b = lvl.apply_host(u)
+    finally:
+        del os.environ["D4B_NO_PIPELINE"]
+    assert np.array_equal(a, b) and np.isfinite(a).all() and np.abs(a).max() > 0
