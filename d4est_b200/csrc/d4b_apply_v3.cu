@@ -296,6 +296,12 @@ __device__ __forceinline__ void v3_flux(const v3_args &A, int code, const v3_fac
   const int tc = code & 7;
   const int64_t g_off = bnd ? __ldg(&fc->g_off) : -1;
   const double wt = c_v3.w[t];
+  /* neighbour-order index of my point (ma,mb) is affine: q0 + ma*sa + mb*sb (see to_nbr_point) */
+  const int f2 = (tc & 2) ? -1 : 1, f4 = (tc & 4) ? -Nq : Nq;
+  const int sa = (tc & 1) ? f2 : f4, sb = (tc & 1) ? f4 : f2;
+  const int q0 = ((tc & 2) ? Nq - 1 : 0) + ((tc & 4) ? Nq * (Nq - 1) : 0);
+  const double *NBt = NB + q0 + t * (FIRST_FIXED ? sa : sb);
+  const int st = FIRST_FIXED ? sb : sa;
 #pragma unroll
   for (int i = 0; i < Nq; i++) {
     const int ma = FIRST_FIXED ? t : i, mb = FIRST_FIXED ? i : t;
@@ -303,8 +309,8 @@ __device__ __forceinline__ void v3_flux(const v3_args &A, int code, const v3_fac
     const double qm = a[0][i] * dr[i] + a[1][i] * ds[i] + a[2][i] * dt[i];
     double jump, t1, hs;
     if (!bnd) {
-      const int qn = to_nbr_point<Nq>(tc, ma, mb);
-      jump = ut[i] - NB[qn]; t1 = -0.5 * (qm + NB[Q2 + qn]); hs = -0.5;
+      const double *nb = NBt + i * st;
+      jump = ut[i] - nb[0]; t1 = -0.5 * (qm + nb[Q2]); hs = -0.5;
     } else {
       const double g = (g_off >= 0) ? __ldg(A.bc_g + g_off + ma + Nq * mb) : 0.;
       jump = ut[i] - g; t1 = -qm; hs = -1.0;
