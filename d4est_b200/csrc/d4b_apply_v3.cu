@@ -123,19 +123,30 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 /* Per-slot metadata, resolved once per bucket (v3_build_slots): one coalesced read per element
  * instead of the frec -> hm -> node_off pointer chase. */
 struct v3_face {
-  int64_t fac_off;   /* my record: a-[3][Q2] at +0, sj*sigma at +6 Q2 (interior) / +3 Q2 (boundary) */
+  int64_t fac_off;   /* my record: a-[3][Q2] at +0, a+[3][Q2] at +3 Q2, sj*sigma at +6 Q2 (interior) / +3 Q2 (boundary) */
   int64_t g_off;     /* Dirichlet data offset or -1                                               */
   int64_t nbr_u;     /* >= 0: offset into u;  < 0: -(offset into u_ghost) - 1                      */
-  int64_t nbr_a;     /* offset into fac of the 3 Q2 doubles folded with the neighbour gradient     */
-  int32_t code;      /* bits 0-2 tcode, 3-5 f_p, 6-7 mode: 0 boundary, 1 nbr a- (a+ = -a-), 2 own a+ */
+  int64_t spare;
+  int32_t code;      /* bits 0-2 tcode, 3-5 f_p, 6-7 mode: 0 boundary, else interior face;
+                        bit 8 INTERNAL: the neighbour sits in MY batch, faces me with f^1 and identity
+                        orientation, so its trace comes by warp shuffle from the threads that own it;
+                        bits 9-13: its index in the batch;
+                        bits 14-18 (external faces): staging slot that holds the neighbour trace     */
   int32_t pad;
 };
 struct v3_slot { int64_t node_off, quad_off; v3_face f[6]; };   /* 256 bytes */
 
+__global__ void v3_fill_slot_of(int n, const int32_t *__restrict__ elem_list, int32_t *__restrict__ slot_of)
+{
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < n) slot_of[elem_list[s]] = s;
+}
+
 __global__ void v3_build_slots(int n, const int32_t *__restrict__ elem_list, const int32_t *__restrict__ frec,
                                const int32_t *__restrict__ nrec, const d4b_hm_t *__restrict__ hm,
                                const int64_t *__restrict__ node_off, const int64_t *__restrict__ quad_off,
-                               int n_local, int64_t local_nodes, int Q2, v3_slot *__restrict__ out)
+                               int n_local, int64_t local_nodes, int Q2, const int32_t *__restrict__ slot_of, int epw,
+                               int share, v3_slot *__restrict__ out)
 {
   int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n) return;
@@ -146,21 +157,55 @@ __global__ void v3_build_slots(int n, const int32_t *__restrict__ elem_list, con
     const d4b_hm_t h = hm[frec[6 * s + f]];
     const int nr = nrec[6 * s + f];
     v3_face F;
-    F.fac_off = h.fac_off; F.g_off = h.g_off; F.nbr_u = 0; F.nbr_a = 0; F.pad = 0;
+    F.fac_off = h.fac_off; F.g_off = h.g_off; F.nbr_u = 0; F.spare = 0; F.pad = 0;
     int mode = 0;
     if (h.nbr >= 0) {
       mode = nr >= 0 ? 1 : 2;
       F.nbr_u = h.nbr < n_local ? node_off[h.nbr] : -(node_off[h.nbr] - local_nodes) - 1;
-      F.nbr_a = nr >= 0 ? hm[nr].fac_off : h.fac_off + 3 * Q2;
     }
     F.code = (h.tcode & 7) | ((h.f_p & 7) << 3) | (mode << 6);
+    if (mode == 1 && h.tcode == 1 && h.f_p == (f ^ 1) && share) {
+      const int ns = slot_of[h.nbr];
+      if (ns >= 0 && ns / epw == s / epw) F.code |= (1 << 8) | ((ns % epw) << 9);
+    }
     S.f[f] = F;
   }
   out[s] = S;
 }
 
+/* Staging plan of one batch of `epw` slots: tasks[round][lane] = 8 * (element in batch) + face, or 0xff.
+ * External interior faces (neighbour outside the batch) need their neighbour's nodal values staged and
+ * turned into a trace by one lane each.  If the whole batch has at most `nslot` of them they all go
+ * into round 0 (a Morton-ordered family of 8 has 24); otherwise round d carries faces 2d, 2d+1 of
+ * every element in slot 2 * element + (face & 1), consumed before round d + 1 overwrites them. */
+#define V3_TASK_BYTES 96
+__global__ void v3_build_tasks(int n, int epw, int nslot, v3_slot *__restrict__ slots, uint8_t *__restrict__ tasks)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nb = (n + epw - 1) / epw;
+  if (b >= nb) return;
+  uint8_t *T = tasks + (size_t)b * V3_TASK_BYTES;
+  for (int i = 0; i < V3_TASK_BYTES; i++) T[i] = 0xff;
+  int next = 0;
+  for (int le = 0; le < epw && b * epw + le < n; le++)
+    for (int f = 0; f < 6; f++) {
+      const int c = slots[b * epw + le].f[f].code;
+      if (((c >> 6) & 3) && !((c >> 8) & 1)) next++;
+    }
+  const bool one_round = next <= nslot;
+  next = 0;
+  for (int le = 0; le < epw && b * epw + le < n; le++)
+    for (int f = 0; f < 6; f++) {
+      int &c = slots[b * epw + le].f[f].code;
+      if (!((c >> 6) & 3) || ((c >> 8) & 1)) continue;
+      const int round = one_round ? 0 : (f >> 1), sl = one_round ? next++ : 2 * le + (f & 1);
+      T[32 * round + sl] = (uint8_t)(8 * le + f);
+      c = (c & ~(31 << 14)) | (sl << 14);
+    }
+}
+
 struct v3_args {
-  const v3_slot *slots; const double *G; const double *fac; const double *bc_g;
+  const v3_slot *slots; const uint8_t *tasks; const double *G; const double *fac; const double *bc_g;
   const double *u, *u_ghost; double *Au; int n_list; /* one past the last slot */ int slot_begin;
 };
 
@@ -173,6 +218,8 @@ __device__ __forceinline__ double ldg_pin(const double *p)
   return v;
 }
 
+#define V3_PAIRS(X) X(2, 2) X(2, 4) X(4, 4)
+
 template <int N, int Nq> struct V3 {
   static constexpr int TPE = Nq, EPW = 32 / Nq, Q2 = Nq * Nq, Q3 = Q2 * Nq, N2 = N * N, N3 = N2 * N;
   static constexpr bool SWZ = (N == 4 && Nq == 4);   /* XOR-swizzled 64-double element blocks      */
@@ -180,20 +227,26 @@ template <int N, int Nq> struct V3 {
   static constexpr int EST = SWZ ? 64 : ((Nq * PS + 3) / 4) * 4; /* element stride of X/Y/Z buffers */
   static constexpr int BUF = EPW * EST;
   static constexpr int HTS = EPW * 2 * Q2;
-  static constexpr int TASKD = N3 + 3 * Q2;          /* doubles staged per neighbour face          */
-  static constexpr int SS = TASKD + (((TASKD / 2) % 2 == 0) ? 2 : 0) + (TASKD % 2); /* even, SS/2 odd */
-  static constexpr int NSLOT = 2 * EPW;              /* one round = faces 2r, 2r+1 of all elements */
-  static constexpr int NSS = NSLOT * SS;
-  static constexpr int BARPAD = SS > TASKD ? 0 : 2;  /* the mbarrier sits in the pad of slot 0     */
-  static constexpr int PERWARP = NSS + 3 * BUF + HTS + BARPAD; /* doubles                          */
+  static constexpr int TASKD = N3;                    /* doubles staged per external face: u of the neighbour */
+  static constexpr int TROUT = 4 * Q2;               /* trace written over them: u+, du+/dr, du+/ds, du+/dt  */
+  static constexpr int SD = TASKD > TROUT ? TASKD : TROUT;
+  static constexpr int SS = SD + 2;                  /* even (16-byte bulk copies), SS/2 odd for SD = 16, 64 */
   static constexpr int SM_BYTES = 233472, CTA_RESERVED = 1024;
+  /* staging slots: as many as two CTAs x 4 warps per SM leave room for, at least one round of the
+   * three-round plan (2 per element), at most one per lane */
+  static constexpr int AVAIL = (SM_BYTES / 2 - CTA_RESERVED) / 32 - (3 * BUF + HTS);
+  static constexpr int NS_FIT = AVAIL > 0 ? AVAIL / SS : 0;
+  static constexpr int NSLOT = NS_FIT > 32 ? 32 : (NS_FIT < 2 * EPW ? 2 * EPW : NS_FIT);
+  static constexpr int NSS = NSLOT * SS;
+  static constexpr int BARPAD = 0;                   /* the mbarrier sits in the pad of slot 0     */
+  static constexpr int PERWARP = NSS + 3 * BUF + HTS + BARPAD; /* doubles                          */
   static constexpr bool TWO = 2 * (4 * PERWARP * 8 + CTA_RESERVED) <= SM_BYTES;   /* 2 CTAs x 4 warps */
   static constexpr int WPB_MAX = (SM_BYTES - CTA_RESERVED) / (PERWARP * 8);
   static constexpr int WPB = TWO ? 4 : (WPB_MAX >= 6 ? 6 : (WPB_MAX >= 1 ? WPB_MAX : 1));
   static constexpr int CTAS = TWO ? 2 : 1;
   static constexpr int THREADS = 32 * WPB;
   static constexpr size_t SMEM = (size_t)WPB * PERWARP * 8;
-  static constexpr bool BULK = (N3 % 2 == 0) && (Q2 % 2 == 0);
+  static constexpr bool BULK = (N3 % 2 == 0);
   /* index of (a,b,c) inside the element block of a transposition buffer.  Swizzled form: both the
    * layout-A access (lanes vary a and element) and the layout-C access (lanes vary c and element)
    * touch 16 distinct 8-byte bank pairs per half-warp. */
@@ -218,43 +271,21 @@ template <int Nq> __device__ __forceinline__ int to_my_point(int tc, int qa, int
   return (tc & 1) ? xx + Nq * yy : yy + Nq * xx;
 }
 
-/* One lane builds the neighbour-side trace of one face from the staged slot S = { u_nbr[N^3],
- * a[3][Nq^2] }:  out[q'] = u+ and out[Q2+q'] = sum_l a+_l du+/dr_l at the neighbour's face
- * quadrature points q' (neighbour order).  mode 1: a = a- of the neighbour's own record (a+ = -a-,
- * natural order);  mode 2: a = a+ stored in my record (my point order).  out may alias S. */
+/* One lane turns the staged nodal values S = u_nbr[N^3] of a neighbour into its trace on the shared
+ * face f_p, at the neighbour's face quadrature points q' (neighbour order), written over S:
+ * out[q'] = u+,  out[(1 + l) Q2 + q'] = du+/dr_l in the neighbour's reference directions l = 0..2. */
 template <int N, int Nq>
-__device__ __forceinline__ void v3_nbr_trace(const double *S, int f_p, int tc, int mode, double *out)
+__device__ __forceinline__ void v3_nbr_trace(double *S, int f_p)
 {
-  constexpr int N2 = N * N, N3 = N2 * N, Q2 = Nq * Nq;
+  constexpr int N2 = N * N, Q2 = Nq * Nq;
   const int dp = f_p >> 1;
   const int sa = dp == 0 ? N : 1, sb = dp == 2 ? N : N2, sn = dp == 0 ? 1 : (dp == 1 ? N : N2);
   const int lay = (f_p & 1) ? (N - 1) * sn : 0;
   const double *Dl = c_v3.D + ((f_p & 1) ? (N - 1) * N : 0);
-  double U[Q2], Qv[Q2];
-  {
-    double X[N2], T1[Nq * N];
-#pragma unroll
-    for (int xb = 0; xb < N; xb++)
-#pragma unroll
-      for (int xa = 0; xa < N; xa++) X[xa + N * xb] = S[xa * sa + xb * sb + lay];
-    cx<N, Nq, N, false>(c_v3.B, X, T1); cy<N, Nq, Nq, false>(c_v3.B, T1, U);
-  }
-  const double *An = S + N3;
   const int ia = dp == 0 ? 1 : 0, ib = dp == 2 ? 1 : 2;
+  double U[Q2], DN[Q2];
   {
-    double DA[Q2], DB[Q2];
-    cx<Nq, Nq, Nq, false>(c_v3.Dq, U, DA); cy<Nq, Nq, Nq, false>(c_v3.Dq, U, DB);
-#pragma unroll
-    for (int qb = 0; qb < Nq; qb++)
-#pragma unroll
-      for (int qa = 0; qa < Nq; qa++) {
-        const int q = qa + Nq * qb;
-        const int ix = mode == 1 ? q : to_my_point<Nq>(tc, qa, qb);
-        Qv[q] = An[ia * Q2 + ix] * DA[q] + An[ib * Q2 + ix] * DB[q];
-      }
-  }
-  {
-    double dn[N2], T1[Nq * N], DN[Q2];
+    double dn[N2], T1[Nq * N];
 #pragma unroll
     for (int xb = 0; xb < N; xb++)
 #pragma unroll
@@ -266,36 +297,72 @@ __device__ __forceinline__ void v3_nbr_trace(const double *S, int f_p, int tc, i
         dn[xa + N * xb] = s;
       }
     cx<N, Nq, N, false>(c_v3.B, dn, T1); cy<N, Nq, Nq, false>(c_v3.B, T1, DN);
-#pragma unroll
-    for (int qb = 0; qb < Nq; qb++)
-#pragma unroll
-      for (int qa = 0; qa < Nq; qa++) {
-        const int q = qa + Nq * qb;
-        const int ix = mode == 1 ? q : to_my_point<Nq>(tc, qa, qb);
-        Qv[q] = fma(An[dp * Q2 + ix], DN[q], Qv[q]);
-      }
   }
-  const double sgn = mode == 1 ? -1.0 : 1.0;
+  {
+    double X[N2], T1[Nq * N];
 #pragma unroll
-  for (int q = 0; q < Q2; q++) { out[q] = U[q]; out[Q2 + q] = sgn * Qv[q]; }
+    for (int xb = 0; xb < N; xb++)
+#pragma unroll
+      for (int xa = 0; xa < N; xa++) X[xa + N * xb] = S[xa * sa + xb * sb + lay];
+    cx<N, Nq, N, false>(c_v3.B, X, T1); cy<N, Nq, Nq, false>(c_v3.B, T1, U);
+  }
+  /* every read of S is done: the slot is overwritten from here on */
+#pragma unroll
+  for (int q = 0; q < Q2; q++) { S[q] = U[q]; S[(1 + dp) * Q2 + q] = DN[q]; }
+  {
+    double DA[Q2];
+    cx<Nq, Nq, Nq, false>(c_v3.Dq, U, DA);
+#pragma unroll
+    for (int q = 0; q < Q2; q++) S[(1 + ia) * Q2 + q] = DA[q];
+    cy<Nq, Nq, Nq, false>(c_v3.Dq, U, DA);
+#pragma unroll
+    for (int q = 0; q < Q2; q++) S[(1 + ib) * Q2 + q] = DA[q];
+  }
 }
+
+/* face classes of a code word */
+__device__ __forceinline__ bool v3_is_bnd(int code) { return ((code >> 6) & 3) == 0; }
+__device__ __forceinline__ bool v3_is_int(int code) { return (code >> 8) & 1; }
+__device__ __forceinline__ bool v3_is_ext(int code) { return !v3_is_bnd(code) && !v3_is_int(code); }
 
 /* SIPG flux at the Nq face points a thread owns (…_flux_sipg.c:645-677, Dirichlet :139-191).
  * Points i = 0..Nq-1 have face-local coordinates (ma,mb) = FIRST_FIXED ? (t,i) : (i,t).
  * a[4][Nq]: a-_r, a-_s, a-_t, sj*sigma at the points (loaded by the caller ahead of use).
- * in: own trace ut and reference gradient (dr,ds,dt);  NB: neighbour trace pair (u+ at +0, q+ at +Q2).
+ * in: own trace ut and own flux qm = sum_l a-_l du-/dr_l;  neighbour side up = u+, qp = sum_l a+_l du+/dr_l
+ * at the same points (ignored on the boundary).
  * out: F (tested with v), Hr/Hs/Ht (tested with dv/dr_l). */
 template <int Nq, bool FIRST_FIXED>
-__device__ __forceinline__ void v3_flux(const v3_args &A, int code, const v3_face *fc, const double *NB, int t,
-                                        const double (&a)[4][Nq], const double (&ut)[Nq], const double (&dr)[Nq],
-                                        const double (&ds)[Nq], const double (&dt)[Nq], double (&F)[Nq],
+__device__ __forceinline__ void v3_flux(const v3_args &A, int code, const v3_face *fc, int t,
+                                        const double (&a)[4][Nq], const double (&ut)[Nq], const double (&qm)[Nq],
+                                        const double (&up)[Nq], const double (&qp)[Nq], double (&F)[Nq],
                                         double (&Hr)[Nq], double (&Hs)[Nq], double (&Ht)[Nq])
 {
-  constexpr int Q2 = Nq * Nq;
-  const bool bnd = (code >> 6) == 0;
-  const int tc = code & 7;
+  const bool bnd = v3_is_bnd(code);
   const int64_t g_off = bnd ? __ldg(&fc->g_off) : -1;
   const double wt = c_v3.w[t];
+#pragma unroll
+  for (int i = 0; i < Nq; i++) {
+    const int ma = FIRST_FIXED ? t : i, mb = FIRST_FIXED ? i : t;
+    const double w = wt * c_v3.w[i];
+    double jump, t1, hs;
+    if (!bnd) {
+      jump = ut[i] - up[i]; t1 = -0.5 * (qm[i] + qp[i]); hs = -0.5;
+    } else {
+      const double g = (g_off >= 0) ? __ldg(A.bc_g + g_off + ma + Nq * mb) : 0.;
+      jump = ut[i] - g; t1 = -qm[i]; hs = -1.0;
+    }
+    F[i] = w * (t1 + a[3][i] * jump);
+    const double c = w * hs * jump;
+    Hr[i] = c * a[0][i]; Hs[i] = c * a[1][i]; Ht[i] = c * a[2][i];
+  }
+}
+/* neighbour side of an EXTERNAL face from its staged trace NB (v3_nbr_trace) and my record's a+ at my points */
+template <int Nq, bool FIRST_FIXED>
+__device__ __forceinline__ void v3_ext_side(const double *NB, int code, int t, const double (&ap)[3][Nq],
+                                            double (&up)[Nq], double (&qp)[Nq])
+{
+  constexpr int Q2 = Nq * Nq;
+  const int tc = code & 7;
   /* neighbour-order index of my point (ma,mb) is affine: q0 + ma*sa + mb*sb (see to_nbr_point) */
   const int f2 = (tc & 2) ? -1 : 1, f4 = (tc & 4) ? -Nq : Nq;
   const int sa = (tc & 1) ? f2 : f4, sb = (tc & 1) ? f4 : f2;
@@ -304,34 +371,47 @@ __device__ __forceinline__ void v3_flux(const v3_args &A, int code, const v3_fac
   const int st = FIRST_FIXED ? sb : sa;
 #pragma unroll
   for (int i = 0; i < Nq; i++) {
-    const int ma = FIRST_FIXED ? t : i, mb = FIRST_FIXED ? i : t;
-    const double w = wt * c_v3.w[i];
-    const double qm = a[0][i] * dr[i] + a[1][i] * ds[i] + a[2][i] * dt[i];
-    double jump, t1, hs;
-    if (!bnd) {
-      const double *nb = NBt + i * st;
-      jump = ut[i] - nb[0]; t1 = -0.5 * (qm + nb[Q2]); hs = -0.5;
-    } else {
-      const double g = (g_off >= 0) ? __ldg(A.bc_g + g_off + ma + Nq * mb) : 0.;
-      jump = ut[i] - g; t1 = -qm; hs = -1.0;
-    }
-    F[i] = w * (t1 + a[3][i] * jump);
-    const double c = w * hs * jump;
-    Hr[i] = c * a[0][i]; Hs[i] = c * a[1][i]; Ht[i] = c * a[2][i];
+    const double *nb = NBt + i * st;
+    up[i] = nb[0];
+    qp[i] = ap[0][i] * nb[Q2] + ap[1][i] * nb[2 * Q2] + ap[2][i] * nb[3 * Q2];
   }
 }
-/* the 4 x Nq own-side factors of a face at my points: issued early so the loads overlap the traces */
+/* the own-side factors of a face at my points (and a+ on external faces): issued early so that the
+ * loads overlap the arithmetic before their use */
 template <int Nq, bool FIRST_FIXED>
-__device__ __forceinline__ void v3_load_fac(const v3_args &A, int64_t fac_off, int code, int t, double (&a)[4][Nq])
+__device__ __forceinline__ void v3_load_fac(const v3_args &A, int64_t fac_off, int code, int t, double (&a)[4][Nq],
+                                            double (&ap)[3][Nq])
 {
   constexpr int Q2 = Nq * Nq;
   const double *Fp = A.fac + fac_off;
-  const int sj = ((code >> 6) == 0) ? 3 : 6;
+  const int sj = v3_is_bnd(code) ? 3 : 6;
+  const bool ext = v3_is_ext(code);
 #pragma unroll
   for (int i = 0; i < Nq; i++) {
     const int q = FIRST_FIXED ? t + Nq * i : i + Nq * t;
     a[0][i] = ldg_pin(Fp + q); a[1][i] = ldg_pin(Fp + Q2 + q); a[2][i] = ldg_pin(Fp + 2 * Q2 + q);
     a[3][i] = ldg_pin(Fp + sj * Q2 + q);
+    if (ext) { ap[0][i] = ldg_pin(Fp + 3 * Q2 + q); ap[1][i] = ldg_pin(Fp + 4 * Q2 + q); ap[2][i] = ldg_pin(Fp + 5 * Q2 + q); }
+    else { ap[0][i] = 0.; ap[1][i] = 0.; ap[2][i] = 0.; }
+  }
+}
+/* neighbour side of the two faces (s = 0, 1) of one direction: INTERNAL faces take the partner
+ * element's own trace and flux of its opposite face from the threads that hold them (same t, same
+ * points: identity orientation), a+ = -a- of the neighbour;  EXTERNAL faces read their staged trace */
+template <int Nq, int TPE, bool FIRST_FIXED>
+__device__ __forceinline__ void v3_nbr_side(unsigned mask, int lane, int t, const double *NS, int SS, const int (&code)[2],
+                                            const double (&ut)[2][Nq], const double (&qm)[2][Nq],
+                                            const double (&ap)[2][3][Nq], double (&up)[2][Nq], double (&qp)[2][Nq])
+{
+#pragma unroll
+  for (int s = 0; s < 2; s++) {
+    const int src = v3_is_int(code[s]) ? ((code[s] >> 9) & 31) * TPE + t : lane;
+#pragma unroll
+    for (int i = 0; i < Nq; i++) {
+      up[s][i] = __shfl_sync(mask, ut[s ^ 1][i], src);
+      qp[s][i] = -__shfl_sync(mask, qm[s ^ 1][i], src);
+    }
+    if (v3_is_ext(code[s])) v3_ext_side<Nq, FIRST_FIXED>(NS + ((code[s] >> 14) & 31) * SS, code[s], t, ap[s], up[s], qp[s]);
   }
 }
 
@@ -345,7 +425,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *W = reinterpret_cast<double *>(smraw) + (size_t)warp * L::PERWARP;
   double *NS = W, *BX = NS + L::NSS, *BY = BX + L::BUF, *BZ = BY + L::BUF, *HT = BZ + L::BUF;
-  uint64_t *bar = reinterpret_cast<uint64_t *>(L::BARPAD ? HT + L::HTS : NS + L::TASKD);
+  uint64_t *bar = reinterpret_cast<uint64_t *>(NS + L::SD);
   const int le = lane / TPE, t = lane % TPE;
   const double *B = c_v3.B, *Dq = c_v3.Dq;
 #define TI(a, b, c) L::ti(a, b, c, le)
@@ -360,39 +440,33 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
   const int slot0 = A.slot_begin + batch * EPW;
   const int slot = slot0 + le;
   const bool act = le < EPW && slot < A.n_list;
+  const unsigned amask = __ballot_sync(FULL, act);
   const v3_slot *sl = A.slots + (act ? slot : 0);
   const int64_t noff = act ? __ldg(&sl->node_off) : -1;
 
   /* ---- neighbour staging: round r covers faces 2r, 2r+1 of every element of the batch ---- */
-  int tk_code = 0;
+  const uint8_t *tkb = A.tasks + (size_t)(slot0 / EPW) * V3_TASK_BYTES;
+  int tk = 0xff, tk_fp = 0;
   auto issue_round = [&](int r) -> uint32_t {
-    const int tle = lane >> 1, tf = 2 * r + (lane & 1);
-    const int tslot = slot0 + tle;
-    tk_code = 0;
+    tk = __ldg(tkb + 32 * r + lane);
     uint32_t bytes = 0;
-    const double *su = nullptr, *sa = nullptr;
-    if (lane < 2 * EPW && tslot < A.n_list) {
-      const v3_face *fc = &A.slots[tslot].f[tf];
-      tk_code = __ldg(&fc->code);
-      if (tk_code >> 6) {
-        const int64_t nu = __ldg(&fc->nbr_u);
-        su = nu >= 0 ? A.u + nu : A.u_ghost + (-nu - 1);
-        sa = A.fac + __ldg(&fc->nbr_a);
-        if (L::BULK && ((((uintptr_t)su) | ((uintptr_t)sa)) & 15) == 0) bytes = (N3 + 3 * Q2) * 8;
-      }
+    const double *su = nullptr;
+    if (tk != 0xff) {
+      const v3_face *fc = &A.slots[slot0 + (tk >> 3)].f[tk & 7];
+      const int64_t nu = __ldg(&fc->nbr_u);
+      tk_fp = (__ldg(&fc->code) >> 3) & 7;
+      su = nu >= 0 ? A.u + nu : A.u_ghost + (-nu - 1);
+      if (L::BULK && (((uintptr_t)su) & 15) == 0) bytes = N3 * 8;
     }
     const uint32_t total = __reduce_add_sync(FULL, bytes);
     if (lane == 0 && total) mbar_expect_tx(bar, total);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncwarp();
-    if (tk_code >> 6) {
+    if (tk != 0xff) {
       double *dst = NS + lane * SS;
-      if (bytes) {
-        bulk_g2s(dst, su, N3 * 8, bar);
-        bulk_g2s(dst + N3, sa, 3 * Q2 * 8, bar);
-      } else { /* unaligned source (odd sizes): plain copy by the owning lane */
+      if (bytes) bulk_g2s(dst, su, N3 * 8, bar);
+      else /* unaligned source (odd sizes): plain copy by the owning lane */
         for (int i = 0; i < N3; i++) dst[i] = __ldg(su + i);
-        for (int i = 0; i < 3 * Q2; i++) dst[N3 + i] = __ldg(sa + i);
-      }
     }
     return total;
   };
@@ -404,8 +478,9 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
     for (int o = t * 128; o < 6 * Q3 * 8; o += TPE * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
     for (int f = t; f < 6; f += TPE) {
       const char *p = reinterpret_cast<const char *>(A.fac + __ldg(&sl->f[f].fac_off));
+      const bool ext = v3_is_ext(__ldg(&sl->f[f].code));
       for (int o = 0; o < 7 * Q2 * 8; o += 128)
-        if (o < 3 * Q2 * 8 || o + 128 > 6 * Q2 * 8) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+        if (ext || o < 3 * Q2 * 8 || o + 128 > 6 * Q2 * 8) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
     }
   }
 
@@ -470,10 +545,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
   for (int r = 0; r < 3; r++) {
     if (tot) { mbar_wait(bar, npar); npar ^= 1; }
     __syncwarp();
-    if (tk_code >> 6) {
-      double *S = NS + lane * SS;
-      v3_nbr_trace<N, Nq>(S, (tk_code >> 3) & 7, tk_code & 7, tk_code >> 6, S);
-    }
+    if (tk != 0xff) v3_nbr_trace<N, Nq>(NS + lane * SS, tk_fp);
     __syncwarp();
     if (r == 0) {
       /* C0 (layout C): thread c = t holds (a,b): faces 0,1 (normal r), then g_r -> BY (T4) */
@@ -486,11 +558,12 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
         for (int b = 0; b < Nq; b++)
 #pragma unroll
           for (int a = 0; a < Nq; a++) { uC[a + Nq * b] = Xe[TI(a, b, t)]; rC[a + Nq * b] = 0.; }
+        double fa[2][4][Nq], ap[2][3][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
+#pragma unroll
+        for (int s = 0; s < 2; s++) v3_load_fac<Nq, false>(A, foff[s], fcode[s], t, fa[s], ap[s]);
 #pragma unroll
         for (int s = 0; s < 2; s++) {
-          double fa[4][Nq]; const int code = fcode[s];
-          v3_load_fac<Nq, false>(A, foff[s], code, t, fa);
-          double ut[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+          double dr[Nq], ds[Nq], dt[Nq];
 #pragma unroll
           for (int b = 0; b < Nq; b++) {
             double s0 = 0., s1 = 0., s2 = 0.;
@@ -499,16 +572,23 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
               s0 = fma(c_v3.e[s][a], uC[a + Nq * b], s0); s1 = fma(c_v3.ed[s][a], uC[a + Nq * b], s1);
               s2 = fma(c_v3.e[s][a], Ze[TI(a, b, t)], s2);
             }
-            ut[b] = s0; dr[b] = s1; dt[b] = s2;
+            ut2[s][b] = s0; dr[b] = s1; dt[b] = s2;
           }
 #pragma unroll
           for (int b = 0; b < Nq; b++) {
             double s0 = 0.;
 #pragma unroll
-            for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], ut[m], s0);
+            for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], ut2[s][m], s0);
             ds[b] = s0;
           }
-          v3_flux<Nq, false>(A, code, &sl->f[s], NS + (2 * le + s) * SS, t, fa, ut, dr, ds, dt, F, Hr, Hs, Ht);
+#pragma unroll
+          for (int b = 0; b < Nq; b++) qm2[s][b] = fa[s][0][b] * dr[b] + fa[s][1][b] * ds[b] + fa[s][2][b] * dt[b];
+        }
+        v3_nbr_side<Nq, TPE, false>(amask, lane, t, NS, SS, fcode, ut2, qm2, ap, up, qp);
+#pragma unroll
+        for (int s = 0; s < 2; s++) {
+          double F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+          v3_flux<Nq, false>(A, fcode[s], &sl->f[s], t, fa[s], ut2[s], qm2[s], up[s], qp[s], F, Hr, Hs, Ht);
 #pragma unroll
           for (int b = 0; b < Nq; b++) {
             double s0 = F[b];
@@ -544,29 +624,38 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
           for (int b = 0; b < Nq; b++) {
             ut[b + Nq * c] = Xe[TI(t, b, c)]; gr[b + Nq * c] = Ye[TI(t, b, c)]; rA[b + Nq * c] = 0.;
           }
+        /* faces 2,3: normal s (index b); my points (a=t, c) */
+        double fa[2][4][Nq], ap[2][3][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
 #pragma unroll
-      for (int s = 0; s < 2; s++) { /* faces 2,3: normal s (index b); my points (a=t, c) */
-        double fa[4][Nq]; const int code = fcode[s];
-        v3_load_fac<Nq, true>(A, foff[s], code, t, fa);
-        double tr[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+        for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s], ap[s]);
 #pragma unroll
-        for (int c = 0; c < Nq; c++) {
-          double s0 = 0., s1 = 0., s2 = 0.;
+        for (int s = 0; s < 2; s++) {
+          double dr[Nq], ds[Nq], dt[Nq];
 #pragma unroll
-          for (int b = 0; b < Nq; b++) {
-            s0 = fma(c_v3.e[s][b], ut[b + Nq * c], s0); s1 = fma(c_v3.ed[s][b], ut[b + Nq * c], s1);
-            s2 = fma(c_v3.e[s][b], gr[b + Nq * c], s2);
+          for (int c = 0; c < Nq; c++) {
+            double s0 = 0., s1 = 0., s2 = 0.;
+#pragma unroll
+            for (int b = 0; b < Nq; b++) {
+              s0 = fma(c_v3.e[s][b], ut[b + Nq * c], s0); s1 = fma(c_v3.ed[s][b], ut[b + Nq * c], s1);
+              s2 = fma(c_v3.e[s][b], gr[b + Nq * c], s2);
+            }
+            ut2[s][c] = s0; ds[c] = s1; dr[c] = s2;
           }
-          tr[c] = s0; ds[c] = s1; dr[c] = s2;
-        }
 #pragma unroll
-        for (int c = 0; c < Nq; c++) {
-          double s0 = 0.;
+          for (int c = 0; c < Nq; c++) {
+            double s0 = 0.;
 #pragma unroll
-          for (int m = 0; m < Nq; m++) s0 = fma(Dq[c * Nq + m], tr[m], s0);
-          dt[c] = s0;
+            for (int m = 0; m < Nq; m++) s0 = fma(Dq[c * Nq + m], ut2[s][m], s0);
+            dt[c] = s0;
+          }
+#pragma unroll
+          for (int c = 0; c < Nq; c++) qm2[s][c] = fa[s][0][c] * dr[c] + fa[s][1][c] * ds[c] + fa[s][2][c] * dt[c];
         }
-        v3_flux<Nq, true>(A, code, &sl->f[2 + s], NS + (2 * le + s) * SS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
+        v3_nbr_side<Nq, TPE, true>(amask, lane, t, NS, SS, fcode, ut2, qm2, ap, up, qp);
+#pragma unroll
+      for (int s = 0; s < 2; s++) {
+        double F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+        v3_flux<Nq, true>(A, fcode[s], &sl->f[2 + s], t, fa[s], ut2[s], qm2[s], up[s], qp[s], F, Hr, Hs, Ht);
 #pragma unroll
         for (int c = 0; c < Nq; c++) {
           double s0 = F[c];
@@ -594,9 +683,9 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
     double rA[Q2];
     if (act) {
       double ut[Q2], gr[Q2], hrF[Q2];
-      int64_t foff[4]; int fcode[4];
+      int64_t foff[2]; int fcode[2];
 #pragma unroll
-      for (int f = 2; f < 4; f++) { foff[f] = __ldg(&sl->f[2 + f].fac_off); fcode[f] = __ldg(&sl->f[2 + f].code); }
+      for (int f = 0; f < 2; f++) { foff[f] = __ldg(&sl->f[4 + f].fac_off); fcode[f] = __ldg(&sl->f[4 + f].code); }
 #pragma unroll
       for (int c = 0; c < Nq; c++)
 #pragma unroll
@@ -605,11 +694,13 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
           rA[b + Nq * c] = 0.;
           hrF[b + Nq * c] = c_v3.e[0][b] * Hr23[0][c] + c_v3.e[1][b] * Hr23[1][c];
         }
+      /* faces 4,5: normal t (index c); my points (a=t, b) */
+      double fa[2][4][Nq], ap[2][3][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
 #pragma unroll
-      for (int s = 0; s < 2; s++) { /* faces 4,5: normal t (index c); my points (a=t, b) */
-        double fa[4][Nq]; const int code = fcode[2 + s];
-        v3_load_fac<Nq, true>(A, foff[2 + s], code, t, fa);
-        double tr[Nq], dr[Nq], ds[Nq], dt[Nq], F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+      for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s], ap[s]);
+#pragma unroll
+      for (int s = 0; s < 2; s++) {
+        double dr[Nq], ds[Nq], dt[Nq];
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
           double s0 = 0., s1 = 0., s2 = 0.;
@@ -618,16 +709,23 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
             s0 = fma(c_v3.e[s][c], ut[b + Nq * c], s0); s1 = fma(c_v3.ed[s][c], ut[b + Nq * c], s1);
             s2 = fma(c_v3.e[s][c], gr[b + Nq * c], s2);
           }
-          tr[b] = s0; dt[b] = s1; dr[b] = s2;
+          ut2[s][b] = s0; dt[b] = s1; dr[b] = s2;
         }
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
           double s0 = 0.;
 #pragma unroll
-          for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], tr[m], s0);
+          for (int m = 0; m < Nq; m++) s0 = fma(Dq[b * Nq + m], ut2[s][m], s0);
           ds[b] = s0;
         }
-        v3_flux<Nq, true>(A, code, &sl->f[4 + s], NS + (2 * le + s) * SS, t, fa, tr, dr, ds, dt, F, Hr, Hs, Ht);
+#pragma unroll
+        for (int b = 0; b < Nq; b++) qm2[s][b] = fa[s][0][b] * dr[b] + fa[s][1][b] * ds[b] + fa[s][2][b] * dt[b];
+      }
+      v3_nbr_side<Nq, TPE, true>(amask, lane, t, NS, SS, fcode, ut2, qm2, ap, up, qp);
+#pragma unroll
+      for (int s = 0; s < 2; s++) {
+        double F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
+        v3_flux<Nq, true>(A, fcode[s], &sl->f[4 + s], t, fa[s], ut2[s], qm2[s], up[s], qp[s], F, Hr, Hs, Ht);
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
           double s0 = F[b];
@@ -732,7 +830,6 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
 }
 
 /* ------------------------------------------------------------------ host side */
-#define V3_PAIRS(X) X(2, 2) X(2, 4) X(4, 4)
 
 bool d4b_v3_supported(int N, int Nq)
 {
@@ -784,10 +881,26 @@ static int v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStr
 {
   if (b.v3_slots) return D4B_OK;   /* resolved once: the tables are immutable after create */
   v3_slot *s = nullptr;
-  D4B_CUDA(cudaMalloc((void **)&s, (size_t)b.count * sizeof(v3_slot)));
+  int32_t *slot_of = nullptr;
+  int epw = 0, nslot = 0;
+#define X(a, c) if (b.N == a && b.Nq == c) { epw = V3<a, c>::EPW; nslot = V3<a, c>::NSLOT; }
+  V3_PAIRS(X)
+#undef X
+  if (!epw) { d4b_set_error("v3_prepare_slots: unsupported (N,Nq)"); return D4B_EINVAL; }
+  const int nbatch = (b.count + epw - 1) / epw;
+  /* test switch: no shuffle exchange inside a batch, every interior face is staged (three rounds) */
+  const int share = getenv("D4B_V3_NO_SHARE") == nullptr;
+  D4B_CUDA(cudaMalloc((void **)&s, (size_t)b.count * sizeof(v3_slot) + (size_t)nbatch * V3_TASK_BYTES));
+  D4B_CUDA(cudaMalloc((void **)&slot_of, (size_t)(m->n_local + 1) * sizeof(int32_t)));
+  D4B_CUDA(cudaMemsetAsync(slot_of, 0xff, (size_t)(m->n_local + 1) * sizeof(int32_t), st));
+  v3_fill_slot_of<<<(b.count + 255) / 256, 256, 0, st>>>(b.count, b.elem_list, slot_of);
   v3_build_slots<<<(b.count + 127) / 128, 128, 0, st>>>(b.count, b.elem_list, b.frec, b.nrec, m->hm, m->node_off,
-                                                      m->quad_off, m->n_local, m->local_nodes, b.Nq * b.Nq, s);
+                                                      m->quad_off, m->n_local, m->local_nodes, b.Nq * b.Nq, slot_of,
+                                                      epw, share, s);
+  v3_build_tasks<<<(nbatch + 127) / 128, 128, 0, st>>>(b.count, epw, nslot, s, reinterpret_cast<uint8_t *>(s + b.count));
   D4B_CUDA(cudaGetLastError());
+  D4B_CUDA(cudaStreamSynchronize(st));
+  cudaFree(slot_of);
   const_cast<d4b_fast_bucket &>(b).v3_slots = s;
   return D4B_OK;
 }
@@ -800,7 +913,7 @@ __global__ void v3_range_need(const v3_slot *__restrict__ slots, int n, int chun
   long long mx = 0;
   for (int s = s0 + threadIdx.x; s < s1; s += blockDim.x) {
     long long v = slots[s].node_off;
-    for (int f = 0; f < 6; f++) if ((slots[s].f[f].code >> 6) && slots[s].f[f].nbr_u > v) v = slots[s].f[f].nbr_u;
+    for (int f = 0; f < 6; f++) if (((slots[s].f[f].code >> 6) & 3) && slots[s].f[f].nbr_u > v) v = slots[s].f[f].nbr_u;
     mx = max(mx, v);
   }
   __shared__ long long red[256];
@@ -835,7 +948,7 @@ static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double
   }
   { int rcs = v3_prepare_slots(m, b, st); if (rcs != D4B_OK) return rcs; }
   v3_args A;
-  A.slots = (const v3_slot *)b.v3_slots; A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
+  A.slots = (const v3_slot *)b.v3_slots; A.tasks = reinterpret_cast<const uint8_t *>(A.slots + b.count); A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
   A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.n_list = slot_end; A.slot_begin = slot_begin;
   static int n_sm = 0;
   if (!n_sm) { int dev = 0; D4B_CUDA(cudaGetDevice(&dev)); D4B_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
