@@ -173,19 +173,21 @@ __global__ void v3_build_slots(int n, const int32_t *__restrict__ elem_list, con
   out[s] = S;
 }
 
-/* Staging plan of one batch of `epw` slots: tasks[round][lane] = 8 * (element in batch) + face, or 0xff.
+/* Staging plan of one batch of `epw` slots: tasks[round][lane] = -1 (none) or the source of the copy in one
+ * word, (offset of the neighbour's nodal values << 8) | ghost << 3 | f_p, so that issuing a round costs a
+ * single coalesced load.
  * External interior faces (neighbour outside the batch) need their neighbour's nodal values staged and
  * turned into a trace by one lane each.  If the whole batch has at most `nslot` of them they all go
  * into round 0 (a Morton-ordered family of 8 has 24); otherwise round d carries faces 2d, 2d+1 of
  * every element in slot 2 * element + (face & 1), consumed before round d + 1 overwrites them. */
-#define V3_TASK_BYTES 96
-__global__ void v3_build_tasks(int n, int epw, int nslot, v3_slot *__restrict__ slots, uint8_t *__restrict__ tasks)
+#define V3_TASK_WORDS 96
+__global__ void v3_build_tasks(int n, int epw, int nslot, v3_slot *__restrict__ slots, int64_t *__restrict__ tasks)
 {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   const int nb = (n + epw - 1) / epw;
   if (b >= nb) return;
-  uint8_t *T = tasks + (size_t)b * V3_TASK_BYTES;
-  for (int i = 0; i < V3_TASK_BYTES; i++) T[i] = 0xff;
+  int64_t *T = tasks + (size_t)b * V3_TASK_WORDS;
+  for (int i = 0; i < V3_TASK_WORDS; i++) T[i] = -1;
   int next = 0;
   for (int le = 0; le < epw && b * epw + le < n; le++)
     for (int f = 0; f < 6; f++) {
@@ -196,16 +198,18 @@ __global__ void v3_build_tasks(int n, int epw, int nslot, v3_slot *__restrict__ 
   next = 0;
   for (int le = 0; le < epw && b * epw + le < n; le++)
     for (int f = 0; f < 6; f++) {
-      int &c = slots[b * epw + le].f[f].code;
+      v3_face &F = slots[b * epw + le].f[f];
+      int &c = F.code;
       if (!((c >> 6) & 3) || ((c >> 8) & 1)) continue;
       const int round = one_round ? 0 : (f >> 1), sl = one_round ? next++ : 2 * le + (f & 1);
-      T[32 * round + sl] = (uint8_t)(8 * le + f);
+      const int64_t nu = F.nbr_u;
+      T[32 * round + sl] = ((nu >= 0 ? nu : -nu - 1) << 8) | (nu < 0 ? 8 : 0) | ((c >> 3) & 7);
       c = (c & ~(31 << 14)) | (sl << 14);
     }
 }
 
 struct v3_args {
-  const v3_slot *slots; const uint8_t *tasks; const double *G; const double *fac; const double *bc_g;
+  const v3_slot *slots; const int64_t *tasks; const double *G; const double *fac; const double *bc_g;
   const double *u, *u_ghost; double *Au; int n_list; /* one past the last slot */ int slot_begin;
 };
 
@@ -376,33 +380,30 @@ __device__ __forceinline__ void v3_ext_side(const double *NB, int code, int t, c
     qp[i] = ap[0][i] * nb[Q2] + ap[1][i] * nb[2 * Q2] + ap[2][i] * nb[3 * Q2];
   }
 }
-/* the own-side factors of a face at my points (and a+ on external faces): issued early so that the
- * loads overlap the arithmetic before their use */
+/* the own-side factors of a face at my points: issued early so that the loads overlap the arithmetic
+ * before their use */
 template <int Nq, bool FIRST_FIXED>
-__device__ __forceinline__ void v3_load_fac(const v3_args &A, int64_t fac_off, int code, int t, double (&a)[4][Nq],
-                                            double (&ap)[3][Nq])
+__device__ __forceinline__ void v3_load_fac(const v3_args &A, int64_t fac_off, int code, int t, double (&a)[4][Nq])
 {
   constexpr int Q2 = Nq * Nq;
   const double *Fp = A.fac + fac_off;
   const int sj = v3_is_bnd(code) ? 3 : 6;
-  const bool ext = v3_is_ext(code);
 #pragma unroll
   for (int i = 0; i < Nq; i++) {
     const int q = FIRST_FIXED ? t + Nq * i : i + Nq * t;
     a[0][i] = ldg_pin(Fp + q); a[1][i] = ldg_pin(Fp + Q2 + q); a[2][i] = ldg_pin(Fp + 2 * Q2 + q);
     a[3][i] = ldg_pin(Fp + sj * Q2 + q);
-    if (ext) { ap[0][i] = ldg_pin(Fp + 3 * Q2 + q); ap[1][i] = ldg_pin(Fp + 4 * Q2 + q); ap[2][i] = ldg_pin(Fp + 5 * Q2 + q); }
-    else { ap[0][i] = 0.; ap[1][i] = 0.; ap[2][i] = 0.; }
   }
 }
 /* neighbour side of the two faces (s = 0, 1) of one direction: INTERNAL faces take the partner
  * element's own trace and flux of its opposite face from the threads that hold them (same t, same
  * points: identity orientation), a+ = -a- of the neighbour;  EXTERNAL faces read their staged trace */
 template <int Nq, int TPE, bool FIRST_FIXED>
-__device__ __forceinline__ void v3_nbr_side(unsigned mask, int lane, int t, const double *NS, int SS, const int (&code)[2],
-                                            const double (&ut)[2][Nq], const double (&qm)[2][Nq],
-                                            const double (&ap)[2][3][Nq], double (&up)[2][Nq], double (&qp)[2][Nq])
+__device__ __forceinline__ void v3_nbr_side(const v3_args &A, unsigned mask, int lane, int t, const double *NS, int SS,
+                                            const int (&code)[2], const int64_t (&foff)[2], const double (&ut)[2][Nq],
+                                            const double (&qm)[2][Nq], double (&up)[2][Nq], double (&qp)[2][Nq])
 {
+  constexpr int Q2 = Nq * Nq;
 #pragma unroll
   for (int s = 0; s < 2; s++) {
     const int src = v3_is_int(code[s]) ? ((code[s] >> 9) & 31) * TPE + t : lane;
@@ -411,7 +412,17 @@ __device__ __forceinline__ void v3_nbr_side(unsigned mask, int lane, int t, cons
       up[s][i] = __shfl_sync(mask, ut[s ^ 1][i], src);
       qp[s][i] = -__shfl_sync(mask, qm[s ^ 1][i], src);
     }
-    if (v3_is_ext(code[s])) v3_ext_side<Nq, FIRST_FIXED>(NS + ((code[s] >> 14) & 31) * SS, code[s], t, ap[s], up[s], qp[s]);
+    if (v3_is_ext(code[s])) {
+      /* a+ of my record at my points (L2-resident: prefetched at the start of the batch) */
+      double ap[3][Nq];
+      const double *Fp = A.fac + foff[s] + 3 * Q2;
+#pragma unroll
+      for (int i = 0; i < Nq; i++) {
+        const int q = FIRST_FIXED ? t + Nq * i : i + Nq * t;
+        ap[0][i] = ldg_pin(Fp + q); ap[1][i] = ldg_pin(Fp + Q2 + q); ap[2][i] = ldg_pin(Fp + 2 * Q2 + q);
+      }
+      v3_ext_side<Nq, FIRST_FIXED>(NS + ((code[s] >> 14) & 31) * SS, code[s], t, ap, up[s], qp[s]);
+    }
   }
 }
 
@@ -445,24 +456,21 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
   const int64_t noff = act ? __ldg(&sl->node_off) : -1;
 
   /* ---- neighbour staging: round r covers faces 2r, 2r+1 of every element of the batch ---- */
-  const uint8_t *tkb = A.tasks + (size_t)(slot0 / EPW) * V3_TASK_BYTES;
-  int tk = 0xff, tk_fp = 0;
+  const int64_t *tkb = A.tasks + (size_t)(slot0 / EPW) * V3_TASK_WORDS;
+  int64_t tk = -1;
   auto issue_round = [&](int r) -> uint32_t {
     tk = __ldg(tkb + 32 * r + lane);
     uint32_t bytes = 0;
     const double *su = nullptr;
-    if (tk != 0xff) {
-      const v3_face *fc = &A.slots[slot0 + (tk >> 3)].f[tk & 7];
-      const int64_t nu = __ldg(&fc->nbr_u);
-      tk_fp = (__ldg(&fc->code) >> 3) & 7;
-      su = nu >= 0 ? A.u + nu : A.u_ghost + (-nu - 1);
+    if (tk >= 0) {
+      su = ((tk & 8) ? A.u_ghost : A.u) + (tk >> 8);
       if (L::BULK && (((uintptr_t)su) & 15) == 0) bytes = N3 * 8;
     }
     const uint32_t total = __reduce_add_sync(FULL, bytes);
     if (lane == 0 && total) mbar_expect_tx(bar, total);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncwarp();
-    if (tk != 0xff) {
+    if (tk >= 0) {
       double *dst = NS + lane * SS;
       if (bytes) bulk_g2s(dst, su, N3 * 8, bar);
       else /* unaligned source (odd sizes): plain copy by the owning lane */
@@ -545,7 +553,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
   for (int r = 0; r < 3; r++) {
     if (tot) { mbar_wait(bar, npar); npar ^= 1; }
     __syncwarp();
-    if (tk != 0xff) v3_nbr_trace<N, Nq>(NS + lane * SS, tk_fp);
+    if (tk >= 0) v3_nbr_trace<N, Nq>(NS + lane * SS, (int)(tk & 7));
     __syncwarp();
     if (r == 0) {
       /* C0 (layout C): thread c = t holds (a,b): faces 0,1 (normal r), then g_r -> BY (T4) */
@@ -558,9 +566,9 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
         for (int b = 0; b < Nq; b++)
 #pragma unroll
           for (int a = 0; a < Nq; a++) { uC[a + Nq * b] = Xe[TI(a, b, t)]; rC[a + Nq * b] = 0.; }
-        double fa[2][4][Nq], ap[2][3][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
+        double fa[2][4][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
 #pragma unroll
-        for (int s = 0; s < 2; s++) v3_load_fac<Nq, false>(A, foff[s], fcode[s], t, fa[s], ap[s]);
+        for (int s = 0; s < 2; s++) v3_load_fac<Nq, false>(A, foff[s], fcode[s], t, fa[s]);
 #pragma unroll
         for (int s = 0; s < 2; s++) {
           double dr[Nq], ds[Nq], dt[Nq];
@@ -584,7 +592,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
 #pragma unroll
           for (int b = 0; b < Nq; b++) qm2[s][b] = fa[s][0][b] * dr[b] + fa[s][1][b] * ds[b] + fa[s][2][b] * dt[b];
         }
-        v3_nbr_side<Nq, TPE, false>(amask, lane, t, NS, SS, fcode, ut2, qm2, ap, up, qp);
+        v3_nbr_side<Nq, TPE, false>(A, amask, lane, t, NS, SS, fcode, foff, ut2, qm2, up, qp);
 #pragma unroll
         for (int s = 0; s < 2; s++) {
           double F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
@@ -625,9 +633,9 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
             ut[b + Nq * c] = Xe[TI(t, b, c)]; gr[b + Nq * c] = Ye[TI(t, b, c)]; rA[b + Nq * c] = 0.;
           }
         /* faces 2,3: normal s (index b); my points (a=t, c) */
-        double fa[2][4][Nq], ap[2][3][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
+        double fa[2][4][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
 #pragma unroll
-        for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s], ap[s]);
+        for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s]);
 #pragma unroll
         for (int s = 0; s < 2; s++) {
           double dr[Nq], ds[Nq], dt[Nq];
@@ -651,7 +659,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
 #pragma unroll
           for (int c = 0; c < Nq; c++) qm2[s][c] = fa[s][0][c] * dr[c] + fa[s][1][c] * ds[c] + fa[s][2][c] * dt[c];
         }
-        v3_nbr_side<Nq, TPE, true>(amask, lane, t, NS, SS, fcode, ut2, qm2, ap, up, qp);
+        v3_nbr_side<Nq, TPE, true>(A, amask, lane, t, NS, SS, fcode, foff, ut2, qm2, up, qp);
 #pragma unroll
       for (int s = 0; s < 2; s++) {
         double F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
@@ -695,9 +703,9 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
           hrF[b + Nq * c] = c_v3.e[0][b] * Hr23[0][c] + c_v3.e[1][b] * Hr23[1][c];
         }
       /* faces 4,5: normal t (index c); my points (a=t, b) */
-      double fa[2][4][Nq], ap[2][3][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
+      double fa[2][4][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
 #pragma unroll
-      for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s], ap[s]);
+      for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s]);
 #pragma unroll
       for (int s = 0; s < 2; s++) {
         double dr[Nq], ds[Nq], dt[Nq];
@@ -721,7 +729,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
 #pragma unroll
         for (int b = 0; b < Nq; b++) qm2[s][b] = fa[s][0][b] * dr[b] + fa[s][1][b] * ds[b] + fa[s][2][b] * dt[b];
       }
-      v3_nbr_side<Nq, TPE, true>(amask, lane, t, NS, SS, fcode, ut2, qm2, ap, up, qp);
+      v3_nbr_side<Nq, TPE, true>(A, amask, lane, t, NS, SS, fcode, foff, ut2, qm2, up, qp);
 #pragma unroll
       for (int s = 0; s < 2; s++) {
         double F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
@@ -890,14 +898,14 @@ static int v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStr
   const int nbatch = (b.count + epw - 1) / epw;
   /* test switch: no shuffle exchange inside a batch, every interior face is staged (three rounds) */
   const int share = getenv("D4B_V3_NO_SHARE") == nullptr;
-  D4B_CUDA(cudaMalloc((void **)&s, (size_t)b.count * sizeof(v3_slot) + (size_t)nbatch * V3_TASK_BYTES));
+  D4B_CUDA(cudaMalloc((void **)&s, (size_t)b.count * sizeof(v3_slot) + (size_t)nbatch * V3_TASK_WORDS * sizeof(int64_t)));
   D4B_CUDA(cudaMalloc((void **)&slot_of, (size_t)(m->n_local + 1) * sizeof(int32_t)));
   D4B_CUDA(cudaMemsetAsync(slot_of, 0xff, (size_t)(m->n_local + 1) * sizeof(int32_t), st));
   v3_fill_slot_of<<<(b.count + 255) / 256, 256, 0, st>>>(b.count, b.elem_list, slot_of);
   v3_build_slots<<<(b.count + 127) / 128, 128, 0, st>>>(b.count, b.elem_list, b.frec, b.nrec, m->hm, m->node_off,
                                                       m->quad_off, m->n_local, m->local_nodes, b.Nq * b.Nq, slot_of,
                                                       epw, share, s);
-  v3_build_tasks<<<(nbatch + 127) / 128, 128, 0, st>>>(b.count, epw, nslot, s, reinterpret_cast<uint8_t *>(s + b.count));
+  v3_build_tasks<<<(nbatch + 127) / 128, 128, 0, st>>>(b.count, epw, nslot, s, reinterpret_cast<int64_t *>(s + b.count));
   D4B_CUDA(cudaGetLastError());
   D4B_CUDA(cudaStreamSynchronize(st));
   cudaFree(slot_of);
@@ -948,7 +956,7 @@ static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double
   }
   { int rcs = v3_prepare_slots(m, b, st); if (rcs != D4B_OK) return rcs; }
   v3_args A;
-  A.slots = (const v3_slot *)b.v3_slots; A.tasks = reinterpret_cast<const uint8_t *>(A.slots + b.count); A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
+  A.slots = (const v3_slot *)b.v3_slots; A.tasks = reinterpret_cast<const int64_t *>(A.slots + b.count); A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
   A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.n_list = slot_end; A.slot_begin = slot_begin;
   static int n_sm = 0;
   if (!n_sm) { int dev = 0; D4B_CUDA(cudaGetDevice(&dev)); D4B_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)); }
