@@ -480,11 +480,10 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
   };
   uint32_t tot = issue_round(0);
 
-  /* L2 prefetch of this element's metric block and own face factors (consumed much later) */
+  /* L2 prefetch of the own-side factors of faces 0..3.  Requests are issued close to their use: with 64
+   * elements in flight per SM, everything prefetched at once would not stay in L2 until it is read */
   if (act) {
-    const char *g = reinterpret_cast<const char *>(A.G + 6 * __ldg(&sl->quad_off));
-    for (int o = t * 128; o < 6 * Q3 * 8; o += TPE * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
-    for (int f = t; f < 6; f += TPE) {
+    for (int f = t; f < 4; f += TPE) {
       const char *p = reinterpret_cast<const char *>(A.fac + __ldg(&sl->f[f].fac_off));
       const bool ext = v3_is_ext(__ldg(&sl->f[f].code));
       for (int o = 0; o < 7 * Q2 * 8; o += 128)
@@ -617,6 +616,15 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
           for (int a = 0; a < Nq; a++) { Ye[TI(a, b, t)] = gr[a + Nq * b]; Ze[TI(a, b, t)] = rC[a + Nq * b]; }
       }
       __syncwarp();
+      /* L2 prefetch of the factors of faces 4,5 (the others were requested at the start of the batch) */
+      if (act) {
+    for (int f = 4 + t; f < 6; f += TPE) {
+      const char *p = reinterpret_cast<const char *>(A.fac + __ldg(&sl->f[f].fac_off));
+      const bool ext = v3_is_ext(__ldg(&sl->f[f].code));
+      for (int o = 0; o < 7 * Q2 * 8; o += 128)
+        if (ext || o < 3 * Q2 * 8 || o + 128 > 6 * Q2 * 8) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+    }
+      }
     }
     if (r == 1) {
       /* A1a (layout A): thread a = t holds (b,c): faces 2,3; their lift goes straight into the
@@ -682,6 +690,11 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
           for (int b = 0; b < Nq; b++) Ze[TI(t, b, c)] += rA[b + Nq * c];
       }
       __syncwarp();
+      /* L2 prefetch of the metric block, consumed in the next phase */
+      if (act) {
+        const char *g = reinterpret_cast<const char *>(A.G + 6 * __ldg(&sl->quad_off));
+        for (int o = t * 128; o < 6 * Q3 * 8; o += TPE * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
+      }
     }
     if (r < 2) tot = issue_round(r + 1);
   }
@@ -826,11 +839,25 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
       for (int i = 0; i < N; i++) Ze[TI(i, j, t)] = O[i + N * j];
   }
   __syncwarp();
-#pragma unroll 1
-  for (int ee = 0; ee < EPW; ee++) {
-    const int64_t base = __shfl_sync(FULL, noff, ee * TPE);
-    if (base >= 0)
-      for (int n = lane; n < N3; n += 32) A.Au[base + n] = BZ[ee * EST + L::ti(n % N, (n / N) % N, n / N2, ee)];
+  {
+    constexpr int PL = (N3 + 31) / 32;
+    double ov[EPW][PL];
+#pragma unroll
+    for (int ee = 0; ee < EPW; ee++)
+#pragma unroll
+      for (int m = 0; m < PL; m++) {
+        const int n = lane + 32 * m;
+        ov[ee][m] = n < N3 ? BZ[ee * EST + L::ti(n % N, (n / N) % N, n / N2, ee)] : 0.;
+      }
+#pragma unroll
+    for (int ee = 0; ee < EPW; ee++) {
+      const int64_t base = __shfl_sync(FULL, noff, ee * TPE);
+#pragma unroll
+      for (int m = 0; m < PL; m++) {
+        const int n = lane + 32 * m;
+        if (base >= 0 && n < N3) A.Au[base + n] = ov[ee][m];
+      }
+    }
   }
   __syncwarp();
   } /* batch loop */
