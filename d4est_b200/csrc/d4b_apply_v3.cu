@@ -478,6 +478,10 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
     }
     return total;
   };
+  /* sign words of the round-1 and round-2 tasks: a batch staged in one round (the common case) skips
+   * the later rounds without touching memory again */
+  const int tk1_hi = __ldg(reinterpret_cast<const int *>(tkb + 32 + lane) + 1);
+  const int tk2_hi = __ldg(reinterpret_cast<const int *>(tkb + 64 + lane) + 1);
   uint32_t tot = issue_round(0);
 
   /* L2 prefetch of the own-side factors of faces 0..3.  Requests are issued close to their use: with 64
@@ -696,7 +700,10 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
         for (int o = t * 128; o < 6 * Q3 * 8; o += TPE * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
       }
     }
-    if (r < 2) tot = issue_round(r + 1);
+    if (r < 2) {
+      if (__any_sync(FULL, (tk1_hi & tk2_hi) >= 0)) tot = issue_round(r + 1);
+      else { tot = 0; tk = -1; }
+    }
   }
 
   /* A1b (layout A): faces 4,5, metric, s/t transposed derivatives */
