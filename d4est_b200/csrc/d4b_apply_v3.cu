@@ -572,6 +572,14 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
         double fa[2][4][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
 #pragma unroll
         for (int s = 0; s < 2; s++) v3_load_fac<Nq, false>(A, foff[s], fcode[s], t, fa[s]);
+        { /* g_r = Dq_r ut -> BY (T4), while the factor loads are in flight */
+          double gr[Q2];
+          cx<Nq, Nq, Nq, false>(Dq, uC, gr);
+#pragma unroll
+          for (int b = 0; b < Nq; b++)
+#pragma unroll
+            for (int a = 0; a < Nq; a++) Ye[TI(a, b, t)] = gr[a + Nq * b];
+        }
 #pragma unroll
         for (int s = 0; s < 2; s++) {
           double dr[Nq], ds[Nq], dt[Nq];
@@ -611,13 +619,11 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
             HT[(le * 2 + s) * Q2 + b + Nq * t] = Ht[b];
           }
         }
-        /* g_r = Dq_r ut -> BY (T4);  rC parked in BZ over g_t (same thread, same addresses) */
-        double gr[Q2];
-        cx<Nq, Nq, Nq, false>(Dq, uC, gr);
+        /* rC parked in BZ over g_t (same thread, same addresses) */
 #pragma unroll
         for (int b = 0; b < Nq; b++)
 #pragma unroll
-          for (int a = 0; a < Nq; a++) { Ye[TI(a, b, t)] = gr[a + Nq * b]; Ze[TI(a, b, t)] = rC[a + Nq * b]; }
+          for (int a = 0; a < Nq; a++) Ze[TI(a, b, t)] = rC[a + Nq * b];
       }
       __syncwarp();
       /* L2 prefetch of the factors of faces 4,5 (the others were requested at the start of the batch) */
@@ -1001,7 +1007,7 @@ static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double
    * cache (the kernel is ~100 KB of SASS); D4B_V3_PERSISTENT=1 caps the grid at one CTA per SM */
   static int persist = -1;
   if (persist < 0) persist = getenv("D4B_V3_PERSISTENT") != nullptr;
-  if (persist && grid > n_sm) grid = n_sm;
+  if (persist && grid > n_sm * L::CTAS) grid = n_sm * L::CTAS;
   d4b_apply_v3_kernel<N, Nq><<<grid, L::THREADS, L::SMEM, st>>>(A);
   D4B_CUDA(cudaGetLastError());
   d4b_count_launch(1);
