@@ -454,6 +454,12 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
   const unsigned amask = __ballot_sync(FULL, act);
   const v3_slot *sl = A.slots + (act ? slot : 0);
   const int64_t noff = act ? __ldg(&sl->node_off) : -1;
+  /* record offsets and codes of all six faces and the metric offset, loaded once up front: the factor
+   * loads of a phase then do not wait for a pointer fetch first */
+  int64_t foffs[6]; int fcodes[6];
+#pragma unroll
+  for (int f = 0; f < 6; f++) { foffs[f] = __ldg(&sl->f[f].fac_off); fcodes[f] = __ldg(&sl->f[f].code); }
+  const int64_t qoff = __ldg(&sl->quad_off);
 
   /* ---- neighbour staging: round r covers faces 2r, 2r+1 of every element of the batch ---- */
   const int64_t *tkb = A.tasks + (size_t)(slot0 / EPW) * V3_TASK_WORDS;
@@ -564,7 +570,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
         double uC[Q2], rC[Q2];
         int64_t foff[2]; int fcode[2];
 #pragma unroll
-        for (int s = 0; s < 2; s++) { foff[s] = __ldg(&sl->f[s].fac_off); fcode[s] = __ldg(&sl->f[s].code); }
+        for (int s = 0; s < 2; s++) { foff[s] = foffs[s]; fcode[s] = fcodes[s]; }
 #pragma unroll
         for (int b = 0; b < Nq; b++)
 #pragma unroll
@@ -643,7 +649,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
         double ut[Q2], gr[Q2], rA[Q2];
         int64_t foff[2]; int fcode[2];
 #pragma unroll
-        for (int f = 0; f < 2; f++) { foff[f] = __ldg(&sl->f[2 + f].fac_off); fcode[f] = __ldg(&sl->f[2 + f].code); }
+        for (int f = 0; f < 2; f++) { foff[f] = foffs[2 + f]; fcode[f] = fcodes[2 + f]; }
 #pragma unroll
         for (int c = 0; c < Nq; c++)
 #pragma unroll
@@ -702,7 +708,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
       __syncwarp();
       /* L2 prefetch of the metric block, consumed in the next phase */
       if (act) {
-        const char *g = reinterpret_cast<const char *>(A.G + 6 * __ldg(&sl->quad_off));
+        const char *g = reinterpret_cast<const char *>(A.G + 6 * qoff);
         for (int o = t * 128; o < 6 * Q3 * 8; o += TPE * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
       }
     }
@@ -719,7 +725,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
       double ut[Q2], gr[Q2], hrF[Q2];
       int64_t foff[2]; int fcode[2];
 #pragma unroll
-      for (int f = 0; f < 2; f++) { foff[f] = __ldg(&sl->f[4 + f].fac_off); fcode[f] = __ldg(&sl->f[4 + f].code); }
+      for (int f = 0; f < 2; f++) { foff[f] = foffs[4 + f]; fcode[f] = fcodes[4 + f]; }
 #pragma unroll
       for (int c = 0; c < Nq; c++)
 #pragma unroll
@@ -780,7 +786,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
         for (int b = 0; b < Nq; b++) { Ze[TI(t, b, c)] += rA[b + Nq * c]; rA[b + Nq * c] = 0.; }
       double gs[Q2], gt[Q2];
       cx<Nq, Nq, Nq, false>(Dq, ut, gs); cy<Nq, Nq, Nq, false>(Dq, ut, gt);
-      const double *Ge = A.G + 6 * __ldg(&sl->quad_off) + t;
+      const double *Ge = A.G + 6 * qoff + t;
       const double e0 = c_v3.e[0][t], e1 = c_v3.e[1][t];
       const double *HTe = HT + le * 2 * Q2;
 #pragma unroll
