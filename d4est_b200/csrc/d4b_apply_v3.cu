@@ -650,6 +650,9 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
         int64_t foff[2]; int fcode[2];
 #pragma unroll
         for (int f = 0; f < 2; f++) { foff[f] = foffs[2 + f]; fcode[f] = fcodes[2 + f]; }
+        double fa[2][4][Nq];
+#pragma unroll
+        for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s]);
 #pragma unroll
         for (int c = 0; c < Nq; c++)
 #pragma unroll
@@ -657,9 +660,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
             ut[b + Nq * c] = Xe[TI(t, b, c)]; gr[b + Nq * c] = Ye[TI(t, b, c)]; rA[b + Nq * c] = 0.;
           }
         /* faces 2,3: normal s (index b); my points (a=t, c) */
-        double fa[2][4][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
-#pragma unroll
-        for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s]);
+        double ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
 #pragma unroll
         for (int s = 0; s < 2; s++) {
           double dr[Nq], ds[Nq], dt[Nq];
@@ -726,6 +727,9 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
       int64_t foff[2]; int fcode[2];
 #pragma unroll
       for (int f = 0; f < 2; f++) { foff[f] = foffs[4 + f]; fcode[f] = fcodes[4 + f]; }
+      double fa[2][4][Nq];
+#pragma unroll
+      for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s]);
 #pragma unroll
       for (int c = 0; c < Nq; c++)
 #pragma unroll
@@ -735,9 +739,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
           hrF[b + Nq * c] = c_v3.e[0][b] * Hr23[0][c] + c_v3.e[1][b] * Hr23[1][c];
         }
       /* faces 4,5: normal t (index c); my points (a=t, b) */
-      double fa[2][4][Nq], ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
-#pragma unroll
-      for (int s = 0; s < 2; s++) v3_load_fac<Nq, true>(A, foff[s], fcode[s], t, fa[s]);
+      double ut2[2][Nq], qm2[2][Nq], up[2][Nq], qp[2][Nq];
 #pragma unroll
       for (int s = 0; s < 2; s++) {
         double dr[Nq], ds[Nq], dt[Nq];
