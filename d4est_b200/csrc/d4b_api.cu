@@ -190,7 +190,8 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
   free(m->send_node_begin_h); free(m->recv_node_begin_h);
   if (m->stream) cudaStreamDestroy(m->stream);
-  if (m->copy_stream) { cudaStreamDestroy(m->copy_stream); cudaStreamDestroy(m->in_stream); for (int k = 0; k < 16; k++) { cudaEventDestroy(m->ev_out[k]); cudaEventDestroy(m->ev_in[k]); } }
+  if (m->copy_stream) { cudaStreamDestroy(m->copy_stream); cudaStreamDestroy(m->in_stream); for (int k = 0; k < D4B_PIPE_MAX; k++) { cudaEventDestroy(m->ev_out[k]); cudaEventDestroy(m->ev_in[k]); } cudaEventDestroy(m->ev_done);
+    cudaFree(m->pipe_late.elem_list); cudaFree(m->pipe_late.frec); cudaFree(m->pipe_late.nrec); cudaFree(m->pipe_late.v3_slots); }
   free(m);
 }
 
@@ -230,32 +231,63 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
   if (m->n_fast == 1 && m->n_generic == 0 && m->fast[0].count == m->n_local && m->fast[0].nrec && m->n_peers == 0 &&
       d4b_v3_supported(m->fast[0].N, m->fast[0].Nq) && m->n_local >= 8192 && !getenv("D4B_NO_PIPELINE")) {
     const d4b_fast_bucket &b = m->fast[0];
-    const int NCH = 16;
+    int NCH = 16;
+    if (const char *e = getenv("D4B_PIPE_CHUNKS")) { int v = atoi(e); if (v >= 2 && v <= D4B_PIPE_MAX) NCH = v; }
     const int64_t N3 = (int64_t)b.N * b.N * b.N;
     int rc0;
     if (!m->copy_stream) {
       D4B_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
       D4B_CUDA(cudaStreamCreateWithFlags(&m->in_stream, cudaStreamNonBlocking));
-      for (int k = 0; k < NCH; k++) {
+      for (int k = 0; k < D4B_PIPE_MAX; k++) {
         D4B_CUDA(cudaEventCreateWithFlags(&m->ev_out[k], cudaEventDisableTiming));
         D4B_CUDA(cudaEventCreateWithFlags(&m->ev_in[k], cudaEventDisableTiming));
       }
+      D4B_CUDA(cudaEventCreateWithFlags(&m->ev_done, cudaEventDisableTiming));
+      /* range boundaries: equal ranges, multiples of the elements per CTA (measured on the bench brick: 16
+       * ranges beat 8, 24 and 32, and ranges tapering towards the end gained nothing -- the download stream
+       * runs at the duplex PCIe rate and simply ends one to two chunks after the upload) */
       const int per = d4b_v3_elems_per_cta(b.N, b.Nq);
-      m->pipe_chunk = ((m->n_local + NCH - 1) / NCH + per - 1) / per * per;
-      m->pipe_ranges = (m->n_local + m->pipe_chunk - 1) / m->pipe_chunk;
-      if ((rc0 = d4b_v3_range_need(m, b, m->pipe_ranges, m->pipe_chunk, m->pipe_need, m->stream)) != D4B_OK) return rc0;
+      int nr0 = 0;
+      m->pipe_b[0] = 0;
+      for (int k = 0; k < NCH; k++) {
+        int e = k == NCH - 1 ? m->n_local : (int)((int64_t)(k + 1) * m->n_local / NCH / per * per);
+        if (e > m->pipe_b[nr0]) m->pipe_b[++nr0] = e;
+      }
+      m->pipe_ranges = nr0;
+      if ((rc0 = d4b_v3_range_need(m, b, m->pipe_ranges, m->pipe_b, m->pipe_need, m->stream)) != D4B_OK) return rc0;
+      if ((rc0 = d4b_v3_build_late(m, b, m->pipe_ranges, m->pipe_b, 1, &m->pipe_late, m->stream)) != D4B_OK) return rc0;
     }
-    const int chunk = m->pipe_chunk, nr = m->pipe_ranges;
+    const int nr = m->pipe_ranges;
+    /* Elements that read a neighbour more than one chunk ahead (seams of the space-filling curve, a few per
+     * cent) would hold their whole range back until most of u has arrived.  If the kernel can store straight
+     * into the caller's buffer (pinned, device-mapped host memory), they are recomputed in a last launch after
+     * the final upload and the final download, and every range runs as soon as the NEXT chunk is there (what
+     * the early launch computes for them from partial data is overwritten).  Otherwise a range waits for the
+     * last chunk it reads. */
+    double *Au_map = nullptr;
+    if (m->pipe_late.count > 0 && !getenv("D4B_NO_LATE_PASS")) {
+      cudaPointerAttributes pa;
+      if (cudaPointerGetAttributes(&pa, Au_host) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer)
+        Au_map = static_cast<double *>(pa.devicePointer);
+      else
+        cudaGetLastError();
+    }
+    const bool defer = Au_map != nullptr || m->pipe_late.count == 0;
+    const bool trace = getenv("D4B_PIPE_TRACE") != nullptr;
+    cudaEvent_t tv[5];
+    if (trace) { for (int i = 0; i < 5; i++) cudaEventCreate(&tv[i]); cudaEventRecord(tv[0], m->in_stream); }
     for (int k = 0; k < nr; k++) {
-      int s0 = k * chunk, s1 = s0 + chunk < m->n_local ? s0 + chunk : m->n_local;
+      int s0 = m->pipe_b[k], s1 = m->pipe_b[k + 1];
       D4B_CUDA(cudaMemcpyAsync(m->u_stage + s0 * N3, u_host + s0 * N3, (size_t)(s1 - s0) * N3 * sizeof(double),
                                cudaMemcpyHostToDevice, m->in_stream));
       D4B_CUDA(cudaEventRecord(m->ev_in[k], m->in_stream));
     }
+    if (trace) cudaEventRecord(tv[1], m->in_stream);
     int waited = -1;
     for (int k = 0; k < nr; k++) {
-      int s0 = k * chunk, s1 = s0 + chunk < m->n_local ? s0 + chunk : m->n_local;
-      int need = m->pipe_need[k] < k ? k : (m->pipe_need[k] >= nr ? nr - 1 : m->pipe_need[k]);
+      int s0 = m->pipe_b[k], s1 = m->pipe_b[k + 1];
+      int need = defer ? k + 1 : m->pipe_need[k];
+      need = need < k ? k : (need >= nr ? nr - 1 : need);
       if (need > waited) { D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_in[need], 0)); waited = need; }
       if ((rc0 = d4b_launch_v3_range(m, b, m->u_stage, m->Au_stage, m->stream, s0, s1)) != D4B_OK) return rc0;
       D4B_CUDA(cudaEventRecord(m->ev_out[k], m->stream));
@@ -263,9 +295,25 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
       D4B_CUDA(cudaMemcpyAsync(Au_host + s0 * N3, m->Au_stage + s0 * N3, (size_t)(s1 - s0) * N3 * sizeof(double),
                                cudaMemcpyDeviceToHost, m->copy_stream));
     }
+    if (trace) { cudaEventRecord(tv[2], m->stream); cudaEventRecord(tv[3], m->copy_stream); }
+    if (Au_map) {
+      if (waited < nr - 1) D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_in[nr - 1], 0));
+      D4B_CUDA(cudaEventRecord(m->ev_done, m->copy_stream));
+      D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_done, 0));
+      if ((rc0 = d4b_launch_v3(m, m->pipe_late, m->u_stage, Au_map, m->stream)) != D4B_OK) return rc0;
+    }
     D4B_CUDA(cudaStreamSynchronize(m->copy_stream));
     D4B_CUDA(cudaStreamSynchronize(m->stream));
     D4B_CUDA(cudaStreamSynchronize(m->in_stream));
+    if (trace) {
+      cudaEventRecord(tv[4], m->stream); cudaEventSynchronize(tv[4]);
+      float a, b2, c, d;
+      cudaEventElapsedTime(&a, tv[0], tv[1]); cudaEventElapsedTime(&b2, tv[0], tv[2]);
+      cudaEventElapsedTime(&c, tv[0], tv[3]); cudaEventElapsedTime(&d, tv[0], tv[4]);
+      fprintf(stderr, "[d4b pipe] h2d done %.2f ms, early kernels done %.2f, d2h done %.2f, all done %.2f (late elements %d)\n",
+              a, b2, c, d, m->pipe_late.count);
+      for (int i = 0; i < 5; i++) cudaEventDestroy(tv[i]);
+    }
     return D4B_OK;
   }
   D4B_CUDA(cudaMemcpyAsync(m->u_stage, u_host, nb, cudaMemcpyHostToDevice, m->stream));

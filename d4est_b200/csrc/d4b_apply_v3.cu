@@ -18,6 +18,7 @@
  * by one lane per face from the neighbour's nodal values, staged by cp.async.bulk + mbarrier; the
  * neighbour-side factor a+ is read as -a- of the NEIGHBOUR's record (one copy in HBM per side).
  */
+#include <vector>
 #include "d4b_internal.h"
 #include "d4b_ops.h"
 #include <cstdlib>
@@ -961,11 +962,26 @@ static int v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStr
   return D4B_OK;
 }
 
-/* For the host-buffer pipeline: need[k] = index of the last u chunk that range k of the bucket reads (its own
- * elements and their local face neighbours), chunks and ranges being the same equal element ranges. */
-__global__ void v3_range_need(const v3_slot *__restrict__ slots, int n, int chunk, int64_t N3, int *__restrict__ need)
+/* Slot ranges of the host-buffer pipeline: range k = slots [b[k], b[k+1]) */
+struct v3_bounds { int n; int b[D4B_PIPE_MAX + 1]; };
+__device__ __forceinline__ int v3_chunk_of(const v3_bounds &B, int slot)
 {
-  const int k = blockIdx.x, s0 = k * chunk, s1 = min(n, s0 + chunk);
+  int k = 0;
+  while (k + 1 < B.n && slot >= B.b[k + 1]) k++;
+  return k;
+}
+static v3_bounds v3_make_bounds(int n_ranges, const int *bounds)
+{
+  v3_bounds B; B.n = n_ranges;
+  for (int k = 0; k <= n_ranges; k++) B.b[k] = bounds[k];
+  return B;
+}
+
+/* For the host-buffer pipeline: need[k] = index of the last u chunk that range k of the bucket reads (its own
+ * elements and their local face neighbours), chunks and ranges being the same element ranges. */
+__global__ void v3_range_need(const v3_slot *__restrict__ slots, v3_bounds B, int64_t N3, int *__restrict__ need)
+{
+  const int k = blockIdx.x, s0 = B.b[k], s1 = B.b[k + 1];
   long long mx = 0;
   for (int s = s0 + threadIdx.x; s < s1; s += blockDim.x) {
     long long v = slots[s].node_off;
@@ -975,20 +991,79 @@ __global__ void v3_range_need(const v3_slot *__restrict__ slots, int n, int chun
   __shared__ long long red[256];
   red[threadIdx.x] = mx; __syncthreads();
   for (int o = blockDim.x / 2; o > 0; o >>= 1) { if (threadIdx.x < o) red[threadIdx.x] = max(red[threadIdx.x], red[threadIdx.x + o]); __syncthreads(); }
-  if (threadIdx.x == 0) need[k] = (int)((red[0] / N3) / chunk);
+  if (threadIdx.x == 0) need[k] = v3_chunk_of(B, (int)(red[0] / N3));
 }
 
-int d4b_v3_range_need(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, int chunk, int *need_host, cudaStream_t st)
+int d4b_v3_range_need(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, const int *bounds, int *need_host, cudaStream_t st)
 {
   int rc = v3_prepare_slots(m, b, st);
   if (rc != D4B_OK) return rc;
   int *d = nullptr;
   D4B_CUDA(cudaMalloc((void **)&d, n_ranges * sizeof(int)));
-  v3_range_need<<<n_ranges, 256, 0, st>>>((const v3_slot *)b.v3_slots, b.count, chunk, (int64_t)b.N * b.N * b.N, d);
+  v3_range_need<<<n_ranges, 256, 0, st>>>((const v3_slot *)b.v3_slots, v3_make_bounds(n_ranges, bounds), (int64_t)b.N * b.N * b.N, d);
   D4B_CUDA(cudaGetLastError());
   D4B_CUDA(cudaMemcpyAsync(need_host, d, n_ranges * sizeof(int), cudaMemcpyDeviceToHost, st));
   D4B_CUDA(cudaStreamSynchronize(st));
   cudaFree(d);
+  return D4B_OK;
+}
+
+/* For the host-buffer pipeline: the elements of the bucket that read a face neighbour more than `lookahead`
+ * chunks ahead of their own chunk (thin layers at the seams of the space-filling curve) are collected into a
+ * bucket of their own, so that every other element of range k can run as soon as chunk k + lookahead is there. */
+__global__ void v3_mark_late(const v3_slot *__restrict__ slots, int n, v3_bounds B, int64_t N3, int lookahead,
+                             int32_t *__restrict__ flag)
+{
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  int late = 0;
+  const int mine = v3_chunk_of(B, s);
+  for (int f = 0; f < 6; f++) {
+    const v3_face &F = slots[s].f[f];
+    if (((F.code >> 6) & 3) && F.nbr_u >= 0 && v3_chunk_of(B, (int)(F.nbr_u / N3)) > mine + lookahead) late = 1;
+  }
+  flag[s] = late;
+}
+__global__ void v3_gather_late(int n, const int32_t *__restrict__ list, const int32_t *__restrict__ elem,
+                               const int32_t *__restrict__ frec, const int32_t *__restrict__ nrec,
+                               int32_t *__restrict__ elem_o, int32_t *__restrict__ frec_o, int32_t *__restrict__ nrec_o)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int s = list[i];
+  elem_o[i] = elem[s];
+  for (int f = 0; f < 6; f++) { frec_o[6 * i + f] = frec[6 * s + f]; nrec_o[6 * i + f] = nrec[6 * s + f]; }
+}
+
+int d4b_v3_build_late(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, const int *bounds, int lookahead,
+                      d4b_fast_bucket *late, cudaStream_t st)
+{
+  int rc = v3_prepare_slots(m, b, st);
+  if (rc != D4B_OK) return rc;
+  late->N = b.N; late->Nq = b.Nq; late->count = 0;
+  late->elem_list = late->frec = late->nrec = nullptr; late->v3_slots = nullptr;
+  int32_t *flag = nullptr;
+  D4B_CUDA(cudaMalloc((void **)&flag, (size_t)b.count * sizeof(int32_t)));
+  v3_mark_late<<<(b.count + 255) / 256, 256, 0, st>>>((const v3_slot *)b.v3_slots, b.count, v3_make_bounds(n_ranges, bounds),
+                                                      (int64_t)b.N * b.N * b.N, lookahead, flag);
+  D4B_CUDA(cudaGetLastError());
+  std::vector<int32_t> h(b.count), list;
+  D4B_CUDA(cudaMemcpyAsync(h.data(), flag, (size_t)b.count * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  D4B_CUDA(cudaStreamSynchronize(st));
+  for (int s = 0; s < b.count; s++) if (h[s]) list.push_back(s);
+  const int n = (int)list.size();
+  if (n) {
+    D4B_CUDA(cudaMemcpyAsync(flag, list.data(), (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    D4B_CUDA(cudaMalloc((void **)&late->elem_list, (size_t)n * sizeof(int32_t)));
+    D4B_CUDA(cudaMalloc((void **)&late->frec, (size_t)n * 6 * sizeof(int32_t)));
+    D4B_CUDA(cudaMalloc((void **)&late->nrec, (size_t)n * 6 * sizeof(int32_t)));
+    v3_gather_late<<<(n + 255) / 256, 256, 0, st>>>(n, flag, b.elem_list, b.frec, b.nrec, late->elem_list, late->frec,
+                                                    late->nrec);
+    D4B_CUDA(cudaGetLastError());
+    D4B_CUDA(cudaStreamSynchronize(st));
+    late->count = n;
+  }
+  cudaFree(flag);
   return D4B_OK;
 }
 

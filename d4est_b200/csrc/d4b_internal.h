@@ -45,8 +45,10 @@ struct d4b_mesh {
   /* halo lists */
   int n_peers; int32_t *peer_rank_h, *send_begin_h, *recv_begin_h; int32_t *send_elem;
   int64_t *send_node_begin_h, *recv_node_begin_h; double *send_buf; int64_t send_nodes; int64_t *send_off; /* device: offset of each send slot in send_buf */
-  cudaStream_t stream, copy_stream, in_stream; cudaEvent_t ev_out[16], ev_in[16];   /* d4b_apply_host pipeline */
-  int pipe_ranges, pipe_chunk, pipe_need[16];
+  #define D4B_PIPE_MAX 32
+  cudaStream_t stream, copy_stream, in_stream; cudaEvent_t ev_out[D4B_PIPE_MAX], ev_in[D4B_PIPE_MAX], ev_done;   /* d4b_apply_host pipeline */
+  int pipe_ranges, pipe_b[D4B_PIPE_MAX + 1], pipe_need[D4B_PIPE_MAX];   /* range k = slots [pipe_b[k], pipe_b[k+1]) */
+  d4b_fast_bucket pipe_late;       /* elements with a face neighbour more than one chunk ahead: computed after the last upload */
   d4b_fast_bucket fast[D4B_MAX_BUCKETS]; int n_fast;
   int32_t *generic_list; int n_generic;   /* elements left to the generic kernel */
 };
@@ -60,7 +62,8 @@ int d4b_launch_v3(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, 
 int d4b_launch_v3_range(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st,
                         int slot_begin, int slot_end);
 int d4b_v3_elems_per_cta(int N, int Nq);
-int d4b_v3_range_need(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, int chunk, int *need_host, cudaStream_t st);
+int d4b_v3_build_late(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, const int *bounds, int lookahead, d4b_fast_bucket *late, cudaStream_t st);
+int d4b_v3_range_need(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, const int *bounds, int *need_host, cudaStream_t st);
 /* split elements into fast buckets + generic list; D->hm == NULL means the uniform device-built brick */
 int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D);
 

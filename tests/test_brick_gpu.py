@@ -65,3 +65,40 @@ def test_host_pipeline_equals_plain_host_path():
     finally:
         del os.environ["D4B_NO_PIPELINE"]
     assert np.array_equal(a, b) and np.isfinite(a).all() and np.abs(a).max() > 0
+
+
+def test_host_pipeline_late_pass_with_pinned_buffers():
+    """With pinned (device-mapped) caller buffers the pipeline defers the elements that read a neighbour more than
+    one chunk ahead to a last launch that stores straight into the caller's Au (d4b_apply_host); D4B_NO_LATE_PASS=1
+    makes every range wait for the last chunk it reads instead.  The deferred elements go through the kernel's
+    three-round staging plan (a+ of their own record instead of -a- of the neighbour): equal to rounding."""
+    import ctypes
+    import os
+    from d4est_b200 import capi
+    L = capi.lib()
+    lvl = d4est_b200.MeshLevel.brick((40, 36, 44), deg=3)   # 63 360 elements, 16 ranges, Morton seams inside
+    n = lvl.local_nodes
+    hp, hq = ctypes.c_void_p(), ctypes.c_void_p()
+    capi.check(L.d4b_host_alloc_pinned(n * 8, ctypes.byref(hp)))
+    capi.check(L.d4b_host_alloc_pinned(n * 8, ctypes.byref(hq)))
+    try:
+        hu = np.ctypeslib.as_array(ctypes.cast(hp, ctypes.POINTER(ctypes.c_double)), shape=(n,))
+        hAu = np.ctypeslib.as_array(ctypes.cast(hq, ctypes.POINTER(ctypes.c_double)), shape=(n,))
+        hu[:] = np.random.default_rng(11).uniform(-1, 1, n)
+        for _ in range(3):                       # repeated: stale data of the previous apply must not leak
+            hAu[:] = np.nan
+            lvl.apply_host(hu, out=hAu)
+            a = hAu.copy()
+            assert np.isfinite(a).all()
+        os.environ["D4B_NO_LATE_PASS"] = "1"
+        try:
+            hAu[:] = np.nan
+            lvl.apply_host(hu, out=hAu)
+            b = hAu.copy()
+        finally:
+            del os.environ["D4B_NO_LATE_PASS"]
+        ref = lvl.apply_host(np.array(hu))       # pageable buffers: no late pass
+        assert np.array_equal(b, ref)
+        assert np.linalg.norm(a - ref) <= 1e-13 * np.linalg.norm(ref)
+    finally:
+        capi.check(L.d4b_host_free_pinned(hp)); capi.check(L.d4b_host_free_pinned(hq))
