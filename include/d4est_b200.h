@@ -133,7 +133,9 @@ int d4b_brick_create_slab(const d4b_brick_params_t *p, int rank, int nranks, d4b
 
 /* ---- operator apply: replaces d4est_laplacian_with_opt_apply_aij
  *      (dGMath/d4est_laplacian_with_opt.c:289) and its twin d4est_laplacian_apply_aij
- *      (dGMath/d4est_laplacian.c:317).  Au is overwritten.                            */
+ *      (dGMath/d4est_laplacian.c:317).  Au is overwritten.
+ *      d4b_apply_host takes any host memory; buffers from d4b_host_alloc_pinned (or cudaHostAlloc /
+ *      cudaHostRegister with the mapped flag) let uploads, kernels and downloads overlap fully.      */
 int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host);
 int d4b_apply_dev(d4b_mesh_t *m, const double *u_dev, double *Au_dev, void *cuda_stream);
 /* ghost values supplied by the caller (single-process tests of the N>1 layout) */
