@@ -787,26 +787,34 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
       for (int c = 0; c < Nq; c++)
 #pragma unroll
         for (int b = 0; b < Nq; b++) { Ze[TI(t, b, c)] += rA[b + Nq * c]; rA[b + Nq * c] = 0.; }
+      /* rows of G are double-buffered: row 0 is requested before g_s, g_t are computed, row c + 1 before
+       * row c is used */
+      const double *Ge = A.G + 6 * qoff + t;
+      double Gv[2][6][Nq];
+      auto load_row = [&](double (&R)[6][Nq], int c) {
+#pragma unroll
+        for (int k = 0; k < 6; k++)
+#pragma unroll
+          for (int b = 0; b < Nq; b++) R[k][b] = ldg_pin(Ge + k * Q3 + Nq * (b + Nq * c));
+      };
+      load_row(Gv[0], 0);
+      asm volatile("" ::: "memory");
       double gs[Q2], gt[Q2];
       cx<Nq, Nq, Nq, false>(Dq, ut, gs); cy<Nq, Nq, Nq, false>(Dq, ut, gt);
-      const double *Ge = A.G + 6 * qoff + t;
       const double e0 = c_v3.e[0][t], e1 = c_v3.e[1][t];
       const double *HTe = HT + le * 2 * Q2;
 #pragma unroll
       for (int c = 0; c < Nq; c++) {
-        double Gv[6][Nq];
-#pragma unroll
-        for (int k = 0; k < 6; k++)
-#pragma unroll
-          for (int b = 0; b < Nq; b++) Gv[k][b] = ldg_pin(Ge + k * Q3 + Nq * (b + Nq * c));
+        if (c + 1 < Nq) load_row(Gv[(c + 1) & 1], c + 1);
         asm volatile("" ::: "memory");
+        const double (&R)[6][Nq] = Gv[c & 1];
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
           const int i = b + Nq * c;
           const double a = gr[i], bb = gs[i], cc = gt[i];
-          gr[i] = Gv[0][b] * a + Gv[1][b] * bb + Gv[2][b] * cc + hrF[i];
-          gs[i] = Gv[1][b] * a + Gv[3][b] * bb + Gv[4][b] * cc;
-          gt[i] = Gv[2][b] * a + Gv[4][b] * bb + Gv[5][b] * cc + e0 * HTe[i] + e1 * HTe[Q2 + i];
+          gr[i] = R[0][b] * a + R[1][b] * bb + R[2][b] * cc + hrF[i];
+          gs[i] = R[1][b] * a + R[3][b] * bb + R[4][b] * cc;
+          gt[i] = R[2][b] * a + R[4][b] * bb + R[5][b] * cc + e0 * HTe[i] + e1 * HTe[Q2 + i];
         }
       }
       cx_acc<Nq, Nq, Nq, true>(Dq, gs, rA); cy_acc<Nq, Nq, Nq, true>(Dq, gt, rA);
