@@ -14,9 +14,13 @@
  * Thread mapping: Nq threads per element, each holding one PLANE of the element in registers, in
  * two layouts -- A: thread = r-index, plane (s,t);  C: thread = t-index, plane (r,s).  Two of the
  * three contractions are register-local in each layout; the third moves through a per-warp
- * shared-memory transposition (__syncwarp only, no block barriers).  Neighbour traces are built
- * by one lane per face from the neighbour's nodal values, staged by cp.async.bulk + mbarrier; the
- * neighbour-side factor a+ is read as -a- of the NEIGHBOUR's record (one copy in HBM per side).
+ * shared-memory transposition (__syncwarp only, no block barriers).
+ * Neighbour side of a face: if the neighbour is in the same warp batch (opposite face, identity
+ * orientation -- 24 of the 48 faces of a Morton family of 8) its own trace and flux come by warp
+ * shuffle from the threads that hold them and a+ = -a- of the neighbour; otherwise one lane stages
+ * the neighbour's nodal values (cp.async.bulk + mbarrier), turns them into the trace and reference
+ * gradient at the neighbour's face points, and the flux threads fold those with the a+ rows of MY
+ * record.  Batches with few enough external faces are staged in one round, the others in three.
  */
 #include <vector>
 #include "d4b_internal.h"
