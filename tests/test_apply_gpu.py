@@ -72,7 +72,8 @@ def test_register_blocked_kernel_equals_line_kernel_and_generic(name, ref_fixtur
         pytest.skip("reference fixture not built")
     fx = fixture.load(p)
     out = {}
-    for key, env in (("v3", {}), ("v2", {"D4B_NO_V3": "1"}), ("generic", {"D4B_NO_FAST": "1"})):
+    for key, env in (("v3", {}), ("v3_three_rounds", {"D4B_V3_NO_SHARE": "1"}), ("v2", {"D4B_NO_V3": "1"}),
+                     ("generic", {"D4B_NO_FAST": "1"})):
         for k, v in env.items():
             os.environ[k] = v
         try:
@@ -86,6 +87,32 @@ def test_register_blocked_kernel_equals_line_kernel_and_generic(name, ref_fixtur
     for key in out:
         assert rel(out[key], fx["Au_ref_with_opt"]) < TOL, key
     assert rel(out["v3"], out["v2"]) < 1e-13 and rel(out["v3"], out["generic"]) < 1e-13
+    assert rel(out["v3"], out["v3_three_rounds"]) < 1e-13
+
+
+@pytest.mark.parametrize("dims,deg", [((5, 3, 7), 3), ((9, 9, 9), 3), ((17, 4, 3), 1), ((6, 10, 2), 1), ((2, 2, 2), 3)])
+def test_register_blocked_kernel_on_odd_bricks(dims, deg):
+    """Bricks whose element count is not a multiple of the warp batch and whose Morton families are incomplete
+    (odd extents): the shuffle exchange / one-round staging plan, the three-round plan and the line-task kernel
+    agree to round-off, and the result is bitwise repeatable."""
+    out = {}
+    u = None
+    for key, env in (("v3", {}), ("v3_three_rounds", {"D4B_V3_NO_SHARE": "1"}), ("v2", {"D4B_NO_V3": "1"})):
+        for k, v in env.items():
+            os.environ[k] = v
+        try:
+            lvl = d4est_b200.MeshLevel.brick(dims, deg=deg)
+            if u is None:
+                u = np.random.default_rng(5).uniform(-1, 1, lvl.local_nodes)
+            out[key] = lvl.apply_host(u)
+            if key == "v3":
+                assert np.array_equal(out[key], lvl.apply_host(u))
+            lvl.close()
+        finally:
+            for k in env:
+                del os.environ[k]
+    assert np.isfinite(out["v3"]).all() and np.abs(out["v3"]).max() > 0
+    assert rel(out["v3"], out["v2"]) < 1e-13 and rel(out["v3"], out["v3_three_rounds"]) < 1e-13
 
 
 def test_back_to_back_device_applies_on_a_multi_bucket_mesh(golden_dir):
