@@ -126,6 +126,18 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
     }
   };
   if (active) {
+    /* L2 prefetch of the metric block (read after the three interpolation stages) and of the six
+     * face-factor records (read after the whole volume phase) */
+    {
+      const char *g = reinterpret_cast<const char *>(A.G + 6 * A.quad_off[e]);
+      for (int o = lt * 128; o < 6 * Q3 * 8; o += TPE * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
+    }
+    if (lt < 6) {
+      const d4b_hm_t *h = A.hm + fr[lt];
+      const char *p = reinterpret_cast<const char *>(A.fac + h->fac_off);
+      const int bytes = (h->nbr >= 0 ? 7 : 4) * Q2 * 8;
+      for (int o = 0; o < bytes; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+    }
     prefetch(0);
 #pragma unroll
     for (int m = 0; m < N3 / TPE; m++) { /* g = lt + TPE m = (i,j) + N2 k */
