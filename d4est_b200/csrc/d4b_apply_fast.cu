@@ -26,6 +26,8 @@ struct fast_args {
   const d4b_hm_t *hm; const double *fac; const double *bc_g;
   const double *u, *u_ghost; double *Au; const int32_t *elem_list; int n_list; int n_local;
   int64_t local_nodes;
+  const v3_slot *slots;   /* per-slot metadata resolved once per bucket (d4b_v3_prepare_slots): one read instead of
+                             the frec -> hm -> node_off chase */
 };
 
 /* out_k[o] = sum_i M_k[o*NI+i] in[i]   (TR: M_k[i*NO+o], i.e. transposed use of an NI x NO table) */
@@ -99,12 +101,11 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
   const int le = threadIdx.x / TPE, lt = threadIdx.x % TPE;
   const int slot = blockIdx.x * L::EPB + le;
   const bool active = slot < A.n_list;
-  const int e = active ? A.elem_list[slot] : 0;
+  const v3_slot *sl = A.slots + (active ? slot : 0);
   double *U = sm + le * L::PER, *ACC = U + L::UA, *S = ACC + L::UA;
   double *V0 = S, *V1 = S + L::AB, *V2 = S + 2 * L::AB, *V3 = V2 + L::BB, *V4 = V3 + L::BB;
   const double *B = c_ft.B, *C = c_ft.C, *D = c_ft.D;
-  const double *ue = A.u + A.node_off[e];
-  const int32_t *fr = frec + 6 * (active ? slot : 0);
+  const double *ue = A.u + __ldg(&sl->node_off);
   const int fa = lt % N, fb = lt / N; /* my face node (T stage) */
 
   /* neighbour normal lines of direction d, prefetched into registers one direction ahead */
@@ -113,11 +114,12 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
   auto prefetch = [&](int d) {
 #pragma unroll
     for (int s = 0; s < 2; s++) {
-      const d4b_hm_t *h = A.hm + fr[2 * d + s];
-      int nb = h->nbr; nlay[s] = -1;
-      if (nb >= 0) {
-        const double *un = (nb < A.n_local) ? A.u + A.node_off[nb] : A.u_ghost + (A.node_off[nb] - A.local_nodes);
-        int fp = h->f_p, dp = fp >> 1; nlay[s] = (fp & 1) ? N - 1 : 0;
+      const v3_face *h = &sl->f[2 * d + s];
+      const int code = __ldg(&h->code); nlay[s] = -1;
+      if ((code >> 6) & 3) {
+        const int64_t nu = __ldg(&h->nbr_u);
+        const double *un = nu >= 0 ? A.u + nu : A.u_ghost + (-nu - 1);
+        int fp = (code >> 3) & 7, dp = fp >> 1; nlay[s] = (fp & 1) ? N - 1 : 0;
         int pa, pb, pn; face_strides(dp, N, N2, pa, pb, pn);
         const double *p = un + fa * pa + fb * pb;
 #pragma unroll
@@ -129,13 +131,13 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
     /* L2 prefetch of the metric block (read after the three interpolation stages) and of the six
      * face-factor records (read after the whole volume phase) */
     {
-      const char *g = reinterpret_cast<const char *>(A.G + 6 * A.quad_off[e]);
+      const char *g = reinterpret_cast<const char *>(A.G + 6 * __ldg(&sl->quad_off));
       for (int o = lt * 128; o < 6 * Q3 * 8; o += TPE * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
     }
     if (lt < 6) {
-      const d4b_hm_t *h = A.hm + fr[lt];
-      const char *p = reinterpret_cast<const char *>(A.fac + h->fac_off);
-      const int bytes = (h->nbr >= 0 ? 7 : 4) * Q2 * 8;
+      const v3_face *h = &sl->f[lt];
+      const char *p = reinterpret_cast<const char *>(A.fac + __ldg(&h->fac_off));
+      const int bytes = (((__ldg(&h->code) >> 6) & 3) ? 7 : 4) * Q2 * 8;
       for (int o = 0; o < bytes; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
     }
     prefetch(0);
@@ -168,7 +170,7 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
   }
   __syncthreads();
   if (active) { /* along r: lines (b,c); metric; transposed r-contraction; in place, in registers */
-    const double *Ge = A.G + 6 * A.quad_off[e];
+    const double *Ge = A.G + 6 * __ldg(&sl->quad_off);
     for (int t = lt; t < Q2; t += TPE) {
       int b = t % Nq, c = t / Nq;
       double Gv[6][Nq];
@@ -266,8 +268,8 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
       for (int t = lt; t < 4 * Nq; t += TPE) {
         int qa = t % Nq, side = t / Nq, s = side & 1;
         if ((side == 2 && nbnd0) || (side == 3 && nbnd1)) continue;
-        const d4b_hm_t *h = A.hm + fr[2 * d + s];
-        const double *F = A.fac + h->fac_off;
+        const v3_face *h = &sl->f[2 * d + s];
+        const double *F = A.fac + __ldg(&h->fac_off);
         const double *in = RB + side * 3 * NQ + qa;
         double x[N], u[Nq], ua[Nq], ub[Nq], un[Nq];
         ld<N>(in, Nq, x); mat1<N, Nq, false>(B, x, u); mat1<N, Nq, false>(C, x, ub);
@@ -283,7 +285,8 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
             o[Q2 + q] = F[ia * Q2 + q] * ua[qb] + F[ib * Q2 + q] * ub[qb] + F[d * Q2 + q] * un[qb];
           }
         } else {
-          const int tc = h->tcode, dp = h->f_p >> 1;
+          const int hc = __ldg(&h->code);
+          const int tc = hc & 7, dp = ((hc >> 3) & 7) >> 1;
           const int ia = dp == 0 ? 1 : 0, ib = dp == 2 ? 1 : 2;
 #pragma unroll
           for (int qb = 0; qb < Nq; qb++) { /* (qa,qb) is the neighbour's point; find mine */
@@ -301,8 +304,8 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
     if (active) {
       for (int t = lt; t < 2 * Q2; t += TPE) {
         int s = t / Q2, q = t % Q2, qa = q % Nq, qb = q / Nq;
-        const d4b_hm_t *h = A.hm + fr[2 * d + s];
-        const double *F = A.fac + h->fac_off;
+        const v3_face *h = &sl->f[2 * d + s];
+        const double *F = A.fac + __ldg(&h->fac_off);
         const bool bnd = s ? nbnd1 : nbnd0;
         double am0 = F[q], am1 = F[Q2 + q], am2 = F[2 * Q2 + q], sjs = F[(bnd ? 3 : 6) * Q2 + q];
         double w = c_ft.w[qa] * c_ft.w[qb];
@@ -311,7 +314,8 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
         if (!bnd) {
           jump = um - RA[(4 + 2 * s) * Q2 + q]; t1 = -0.5 * (qm + RA[(5 + 2 * s) * Q2 + q]); hs = -0.5;
         } else {
-          double g = (h->g_off >= 0) ? A.bc_g[h->g_off + q] : 0.;
+          const int64_t go = __ldg(&h->g_off);
+          double g = (go >= 0) ? A.bc_g[go + q] : 0.;
           jump = um - g; t1 = -qm; hs = -1.0;
         }
         double *fh = RB + s * 4 * Q2 + q;
@@ -370,7 +374,7 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
   }
   __syncthreads();
   if (active) {
-    double *Aue = A.Au + A.node_off[e];
+    double *Aue = A.Au + __ldg(&sl->node_off);
 #pragma unroll
     for (int m = 0; m < N3 / TPE; m++) Aue[lt + TPE * m] = ACC[(lt % N) + SJ * (lt / N) + SK * m];
   }
@@ -390,7 +394,9 @@ static int launch_bucket(const d4b_mesh *m, const d4b_fast_bucket &b, const doub
     D4B_CUDA(cudaFuncSetAttribute(d4b_apply_fast_kernel<N, Nq>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr = true;
   }
+  { int rcs = d4b_v3_prepare_slots(m, b, st); if (rcs != D4B_OK) return rcs; }
   fast_args A;
+  A.slots = (const v3_slot *)b.v3_slots;
   A.node_off = m->node_off; A.quad_off = m->quad_off; A.G = m->G; A.hm_begin = m->hm_begin; A.hm = m->hm;
   A.fac = m->fac; A.bc_g = m->bc_g; A.u = u; A.u_ghost = m->u_ghost; A.Au = Au;
   A.elem_list = b.elem_list; A.n_list = b.count; A.n_local = m->n_local; A.local_nodes = m->local_nodes;

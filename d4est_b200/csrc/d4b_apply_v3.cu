@@ -125,21 +125,6 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
                : "memory");
 }
 
-/* Per-slot metadata, resolved once per bucket (v3_build_slots): one coalesced read per element
- * instead of the frec -> hm -> node_off pointer chase. */
-struct v3_face {
-  int64_t fac_off;   /* my record: a-[3][Q2] at +0, a+[3][Q2] at +3 Q2, sj*sigma at +6 Q2 (interior) / +3 Q2 (boundary) */
-  int64_t g_off;     /* Dirichlet data offset or -1                                               */
-  int64_t nbr_u;     /* >= 0: offset into u;  < 0: -(offset into u_ghost) - 1                      */
-  int64_t spare;
-  int32_t code;      /* bits 0-2 tcode, 3-5 f_p, 6-7 mode: 0 boundary, else interior face;
-                        bit 8 INTERNAL: the neighbour sits in MY batch, faces me with f^1 and identity
-                        orientation, so its trace comes by warp shuffle from the threads that own it;
-                        bits 9-13: its index in the batch;
-                        bits 14-18 (external faces): staging slot that holds the neighbour trace     */
-  int32_t pad;
-};
-struct v3_slot { int64_t node_off, quad_off; v3_face f[6]; };   /* 256 bytes */
 
 __global__ void v3_fill_slot_of(int n, const int32_t *__restrict__ elem_list, int32_t *__restrict__ slot_of)
 {
@@ -160,7 +145,7 @@ __global__ void v3_build_slots(int n, const int32_t *__restrict__ elem_list, con
   S.node_off = node_off[e]; S.quad_off = quad_off[e];
   for (int f = 0; f < 6; f++) {
     const d4b_hm_t h = hm[frec[6 * s + f]];
-    const int nr = nrec[6 * s + f];
+    const int nr = nrec ? nrec[6 * s + f] : -2;
     v3_face F;
     F.fac_off = h.fac_off; F.g_off = h.g_off; F.nbr_u = 0; F.spare = 0; F.pad = 0;
     int mode = 0;
@@ -946,6 +931,9 @@ static int v3_upload_tab(int qt, int N, int Nq, cudaStream_t st)
   return D4B_OK;
 }
 
+static int v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStream_t st);
+int d4b_v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStream_t st) { return v3_prepare_slots(m, b, st); }
+
 static int v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStream_t st)
 {
   if (b.v3_slots) return D4B_OK;   /* resolved once: the tables are immutable after create */
@@ -955,10 +943,12 @@ static int v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStr
 #define X(a, c) if (b.N == a && b.Nq == c) { epw = V3<a, c>::EPW; nslot = V3<a, c>::NSLOT; }
   V3_PAIRS(X)
 #undef X
-  if (!epw) { d4b_set_error("v3_prepare_slots: unsupported (N,Nq)"); return D4B_EINVAL; }
-  const int nbatch = (b.count + epw - 1) / epw;
+  const bool plan = epw != 0;   /* staging plan only for the pairs the register-blocked kernel has; the slot table
+                                   alone also serves the line-task kernel (d4b_apply_fast.cu) */
+  if (!plan) epw = 1;
+  const int nbatch = plan ? (b.count + epw - 1) / epw : 0;
   /* test switch: no shuffle exchange inside a batch, every interior face is staged (three rounds) */
-  const int share = getenv("D4B_V3_NO_SHARE") == nullptr;
+  const int share = plan && getenv("D4B_V3_NO_SHARE") == nullptr;
   D4B_CUDA(cudaMalloc((void **)&s, (size_t)b.count * sizeof(v3_slot) + (size_t)nbatch * V3_TASK_WORDS * sizeof(int64_t)));
   D4B_CUDA(cudaMalloc((void **)&slot_of, (size_t)(m->n_local + 1) * sizeof(int32_t)));
   D4B_CUDA(cudaMemsetAsync(slot_of, 0xff, (size_t)(m->n_local + 1) * sizeof(int32_t), st));
@@ -966,7 +956,7 @@ static int v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStr
   v3_build_slots<<<(b.count + 127) / 128, 128, 0, st>>>(b.count, b.elem_list, b.frec, b.nrec, m->hm, m->node_off,
                                                       m->quad_off, m->n_local, m->local_nodes, b.Nq * b.Nq, slot_of,
                                                       epw, share, s);
-  v3_build_tasks<<<(nbatch + 127) / 128, 128, 0, st>>>(b.count, epw, nslot, s, reinterpret_cast<int64_t *>(s + b.count));
+  if (plan) v3_build_tasks<<<(nbatch + 127) / 128, 128, 0, st>>>(b.count, epw, nslot, s, reinterpret_cast<int64_t *>(s + b.count));
   D4B_CUDA(cudaGetLastError());
   D4B_CUDA(cudaStreamSynchronize(st));
   cudaFree(slot_of);

@@ -53,6 +53,24 @@ struct d4b_mesh {
   int32_t *generic_list; int n_generic;   /* elements left to the generic kernel */
 };
 
+/* Per-slot metadata, resolved once per bucket (v3_build_slots): one coalesced read per element
+ * instead of the frec -> hm -> node_off pointer chase. */
+struct v3_face {
+  int64_t fac_off;   /* my record: a-[3][Q2] at +0, a+[3][Q2] at +3 Q2, sj*sigma at +6 Q2 (interior) / +3 Q2 (boundary) */
+  int64_t g_off;     /* Dirichlet data offset or -1                                               */
+  int64_t nbr_u;     /* >= 0: offset into u;  < 0: -(offset into u_ghost) - 1                      */
+  int64_t spare;
+  int32_t code;      /* bits 0-2 tcode, 3-5 f_p, 6-7 mode: 0 boundary, else interior face;
+                        bit 8 INTERNAL: the neighbour sits in MY batch, faces me with f^1 and identity
+                        orientation, so its trace comes by warp shuffle from the threads that own it;
+                        bits 9-13: its index in the batch;
+                        bits 14-18 (external faces): staging slot that holds the neighbour trace     */
+  int32_t pad;
+};
+struct v3_slot { int64_t node_off, quad_off; v3_face f[6]; };   /* 256 bytes */
+
+int d4b_v3_prepare_slots(const d4b_mesh *m, const d4b_fast_bucket &b, cudaStream_t st); /* any (N,Nq) */
+
 void d4b_set_error(const char *fmt, ...);
 const d4b_ops_dev *d4b_ops_device(int quad_type); /* lazily built + uploaded */
 void d4b_count_launch(int n);
