@@ -122,6 +122,19 @@ d4b_apply_generic_kernel(const d4b_gen_args A)
   const double *I = pool + ops.idx.I[dg][dq][0];
   const double *ue = A.u + A.node_off[e];
 
+  { /* L2 prefetch of what this element reads once, later: its metric block and the factor records of its
+     * half-mortars (8 threads per record) */
+    const char *g = reinterpret_cast<const char *>(A.G + 6 * A.quad_off[e]);
+    for (int o = threadIdx.x * 128; o < 6 * Nq3 * 8; o += blockDim.x * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
+    const int r1 = A.hm_begin[e + 1];
+    for (int r = A.hm_begin[e] + (threadIdx.x >> 3); r < r1; r += blockDim.x >> 3) {
+      const d4b_hm_t *h = A.hm + r;
+      const int n2 = (h->degq + 1) * (h->degq + 1);
+      const char *p = reinterpret_cast<const char *>(A.fac + h->fac_off);
+      const int bytes = (h->nbr >= 0 ? 7 : 4) * n2 * 8;
+      for (int o = (threadIdx.x & 7) * 128; o < bytes; o += 8 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+    }
+  }
   for (int i = threadIdx.x; i < N3; i += blockDim.x) { su[i] = ue[i]; acc[i] = 0.; }
   __syncthreads();
 
