@@ -228,7 +228,19 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
    * the kernel of range k starts when the last chunk it reads (own elements + face neighbours, computed once per
    * level) has arrived; the device->host copy of a finished range overlaps the following kernels and, PCIe
    * being full duplex, the remaining uploads.  Every element writes only its own nodes of Au. */
-  if (m->n_fast == 1 && m->n_generic == 0 && m->fast[0].count == m->n_local && m->fast[0].nrec && m->n_peers == 0 &&
+  /* can the kernel store straight into the caller's buffer (pinned, device-mapped host memory)? */
+  double *Au_map = nullptr;
+  if (!getenv("D4B_NO_LATE_PASS")) {
+    cudaPointerAttributes pa;
+    if (cudaPointerGetAttributes(&pa, Au_host) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer)
+      Au_map = static_cast<double *>(pa.devicePointer);
+    else
+      cudaGetLastError();
+  }
+  /* with neighbour ranks the pipeline needs the late launch: the elements next to a ghost can only be computed
+   * after the halo exchange, which follows the last upload */
+  if (m->n_fast == 1 && m->n_generic == 0 && m->fast[0].count == m->n_local && m->fast[0].nrec &&
+      (m->n_peers == 0 || Au_map) &&
       d4b_v3_supported(m->fast[0].N, m->fast[0].Nq) && m->n_local >= 8192 && !getenv("D4B_NO_PIPELINE")) {
     const d4b_fast_bucket &b = m->fast[0];
     int NCH = 16;
@@ -264,14 +276,7 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
      * the final upload and the final download, and every range runs as soon as the NEXT chunk is there (what
      * the early launch computes for them from partial data is overwritten).  Otherwise a range waits for the
      * last chunk it reads. */
-    double *Au_map = nullptr;
-    if (m->pipe_late.count > 0 && !getenv("D4B_NO_LATE_PASS")) {
-      cudaPointerAttributes pa;
-      if (cudaPointerGetAttributes(&pa, Au_host) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer)
-        Au_map = static_cast<double *>(pa.devicePointer);
-      else
-        cudaGetLastError();
-    }
+    if (m->pipe_late.count == 0) Au_map = nullptr;
     const bool defer = Au_map != nullptr || m->pipe_late.count == 0;
     const bool trace = getenv("D4B_PIPE_TRACE") != nullptr;
     cudaEvent_t tv[5];
@@ -296,11 +301,13 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
                                cudaMemcpyDeviceToHost, m->copy_stream));
     }
     if (trace) { cudaEventRecord(tv[2], m->stream); cudaEventRecord(tv[3], m->copy_stream); }
-    if (Au_map) {
+    const bool dist = m->n_peers > 0 && d4b_comm_size() > 1;
+    if (Au_map || dist) {
       if (waited < nr - 1) D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_in[nr - 1], 0));
+      if (dist && (rc0 = d4b_halo_exchange(m, m->u_stage, m->stream)) != D4B_OK) return rc0;
       D4B_CUDA(cudaEventRecord(m->ev_done, m->copy_stream));
       D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_done, 0));
-      if ((rc0 = d4b_launch_v3(m, m->pipe_late, m->u_stage, Au_map, m->stream)) != D4B_OK) return rc0;
+      if (Au_map && (rc0 = d4b_launch_v3(m, m->pipe_late, m->u_stage, Au_map, m->stream)) != D4B_OK) return rc0;
     }
     D4B_CUDA(cudaStreamSynchronize(m->copy_stream));
     D4B_CUDA(cudaStreamSynchronize(m->stream));

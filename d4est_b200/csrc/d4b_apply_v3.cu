@@ -1012,7 +1012,8 @@ int d4b_v3_range_need(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges,
 
 /* For the host-buffer pipeline: the elements of the bucket that read a face neighbour more than `lookahead`
  * chunks ahead of their own chunk (thin layers at the seams of the space-filling curve) are collected into a
- * bucket of their own, so that every other element of range k can run as soon as chunk k + lookahead is there. */
+ * bucket of their own, so that every other element of range k can run as soon as chunk k + lookahead is there.
+ * Elements with a ghost neighbour join them (N > 1: the halo exchange follows the last upload). */
 __global__ void v3_mark_late(const v3_slot *__restrict__ slots, int n, v3_bounds B, int64_t N3, int lookahead,
                              int32_t *__restrict__ flag)
 {
@@ -1022,7 +1023,9 @@ __global__ void v3_mark_late(const v3_slot *__restrict__ slots, int n, v3_bounds
   const int mine = v3_chunk_of(B, s);
   for (int f = 0; f < 6; f++) {
     const v3_face &F = slots[s].f[f];
-    if (((F.code >> 6) & 3) && F.nbr_u >= 0 && v3_chunk_of(B, (int)(F.nbr_u / N3)) > mine + lookahead) late = 1;
+    if (!((F.code >> 6) & 3)) continue;
+    if (F.nbr_u < 0) late = 1;   /* ghost neighbour: its values arrive with the halo exchange, after the uploads */
+    else if (v3_chunk_of(B, (int)(F.nbr_u / N3)) > mine + lookahead) late = 1;
   }
   flag[s] = late;
 }
