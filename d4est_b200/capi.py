@@ -59,6 +59,7 @@ SYMBOLS = {
     "d4b_apply_dev": (C.c_int, [_P, _P, _P, _P]),
     "d4b_set_ghost_host": (C.c_int, [_P, _P]),
     "d4b_kernel_launches": (C.c_int64, []),
+    "d4b_mesh_kernel_split": (C.c_int, [_P, C.POINTER(C.c_int64)]),
     "d4b_dev_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
     "d4b_dev_free": (C.c_int, [_P]),
     "d4b_h2d": (C.c_int, [_P, _P, C.c_size_t, _P]),
@@ -258,6 +259,13 @@ class MeshLevel:
     @property
     def resident_bytes(self):
         return int(lib().d4b_mesh_bytes(self.handle))
+
+    @property
+    def kernel_split(self):
+        """(elements in the regular-element kernels, in the templated hp kernel, in the completeness kernel)"""
+        c = (C.c_int64 * 3)()
+        check(lib().d4b_mesh_kernel_split(self.handle, c))
+        return tuple(int(v) for v in c)
 
     def set_ghost(self, ug):
         ug = np.ascontiguousarray(ug, np.float64)

@@ -20,6 +20,7 @@ int d4b_launch_generic(const d4b_mesh *m, const double *u, double *Au, const int
                        int n_list, cudaStream_t st);
 size_t d4b_generic_smem_bytes(int NX, int NQX);
 int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st, int *handled);
+int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_t> &cand, std::vector<int32_t> &rest);
 
 extern "C" {
 
@@ -58,9 +59,11 @@ const d4b_ops_dev *d4b_ops_device(int qt)
   std::vector<double> pool;
   d4b_ops_index &ix = g_ops[qt].idx;
   double buf[D4B_OPS_MAXN * D4B_OPS_MAXN], x[D4B_OPS_MAXN], w[D4B_OPS_MAXN];
+  std::vector<std::vector<double>> Dm(D4B_NDEG);
   for (int dg = 0; dg < D4B_NDEG; dg++) {
     int N = dg + 1;
     if (dg == 0) { buf[0] = 0.; } else d4b_ops_diff(dg, buf);
+    Dm[dg].assign(buf, buf + N * N);
     ix.D[dg] = (int)pool.size(); pool.insert(pool.end(), buf, buf + N * N);
     ix.Dt[dg] = (int)pool.size();
     for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) pool.push_back(buf[j * N + i]);
@@ -73,9 +76,17 @@ const d4b_ops_dev *d4b_ops_device(int qt)
     for (int dq = 0; dq < D4B_NDEGQ; dq++)
       for (int c = 0; c < 3; c++) {
         ix.I[dg][dq][c] = (int)pool.size();
-        if (dg == 0 || (qt == 1 && dq == 0)) { pool.insert(pool.end(), (size_t)(dg + 1) * (dq + 1), 1.0); continue; }
-        d4b_ops_interp(dg, dq, qt, c - 1, buf);
-        pool.insert(pool.end(), buf, buf + (dg + 1) * (dq + 1));
+        const int N = dg + 1, Nq = dq + 1;
+        if (dg == 0 || (qt == 1 && dq == 0)) { for (int i = 0; i < N * Nq; i++) buf[i] = 1.0; }
+        else d4b_ops_interp(dg, dq, qt, c - 1, buf);
+        pool.insert(pool.end(), buf, buf + N * Nq);
+        ix.ID[dg][dq][c] = (int)pool.size();   /* (I D)[q][j] = sum_k I[q][k] D[k][j] */
+        for (int q = 0; q < Nq; q++)
+          for (int j = 0; j < N; j++) {
+            double sacc = 0.;
+            for (int k = 0; k < N; k++) sacc += buf[q * N + k] * Dm[dg][k * N + j];
+            pool.push_back(sacc);
+          }
       }
   double *d = nullptr;
   if (cudaMalloc(&d, pool.size() * sizeof(double)) != cudaSuccess ||
@@ -186,6 +197,7 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost);
   cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
   for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); cudaFree(m->fast[i].nrec); cudaFree(m->fast[i].v3_slots); }
+  for (int i = 0; i < m->n_hp; i++) { cudaFree(m->hp[i].slots); cudaFree(m->hp[i].recs); }
   cudaFree(m->generic_list);
   free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
   free(m->send_node_begin_h); free(m->recv_node_begin_h);
@@ -199,6 +211,14 @@ int64_t d4b_mesh_local_nodes(const d4b_mesh_t *m) { return m->local_nodes; }
 int64_t d4b_mesh_ghost_nodes(const d4b_mesh_t *m) { return m->ghost_nodes; }
 int64_t d4b_mesh_bytes(const d4b_mesh_t *m) { return m->bytes; }
 int64_t d4b_mesh_algorithmic_bytes(const d4b_mesh_t *m) { return m->alg_bytes; }
+
+int d4b_mesh_kernel_split(const d4b_mesh_t *m, int64_t counts[3])
+{
+  counts[0] = counts[1] = 0; counts[2] = m->n_generic;
+  for (int i = 0; i < m->n_fast; i++) counts[0] += m->fast[i].count;
+  for (int i = 0; i < m->n_hp; i++) counts[1] += m->hp[i].count;
+  return D4B_OK;
+}
 
 int d4b_set_ghost_host(d4b_mesh_t *m, const double *ug)
 {
@@ -351,8 +371,9 @@ int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
         slot = (slot == -1 && h.child_m < 0 && h.child_p < 0) ? r : -3; /* -3: hanging / several records */
       }
   }
-  std::vector<int32_t> gen;
-  const bool off = getenv("D4B_NO_FAST") != nullptr;
+  std::vector<int32_t> gen, cand;
+  const bool off = getenv("D4B_NO_FAST") != nullptr || getenv("D4B_ALL_HP") != nullptr;
+  const bool no_hp = getenv("D4B_NO_HP") != nullptr || (getenv("D4B_NO_FAST") != nullptr && !getenv("D4B_ALL_HP"));
   for (int e = 0; e < nl; e++) {
     int dg = D->deg[e], dq = D->degq[e];
     bool ok = !off && d4b_fast_supported(dg + 1, dq + 1);
@@ -368,7 +389,7 @@ int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
     } else if (ok) {
       for (int f = 0; f < 6; f++) rec[f] = 6 * e + f; /* device-built brick: records in face order */
     }
-    if (!ok) { gen.push_back(e); continue; }
+    if (!ok) { (no_hp ? gen : cand).push_back(e); continue; }
     int k = dg * D4B_NDEGQ + dq;
     int32_t nrc[6];
     for (int f = 0; f < 6; f++) {
@@ -386,7 +407,7 @@ int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
   int64_t dummy = 0; int rc;
   for (int k = 0; k < D4B_NDEG * D4B_NDEGQ; k++) {
     if (el[k].empty()) continue;
-    if (m->n_fast == D4B_MAX_BUCKETS) { gen.insert(gen.end(), el[k].begin(), el[k].end()); continue; }
+    if (m->n_fast == D4B_MAX_BUCKETS) { d4b_set_error("more than %d (deg, deg_quad) pairs on one level", D4B_MAX_BUCKETS); return D4B_EINVAL; }
     d4b_fast_bucket &b = m->fast[m->n_fast++];
     b.N = k / D4B_NDEGQ + 1; b.Nq = k % D4B_NDEGQ + 1; b.count = (int)el[k].size();
     if ((rc = upload(&b.elem_list, el[k].data(), el[k].size(), &dummy)) != D4B_OK) return rc;
@@ -394,6 +415,7 @@ int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
     b.nrec = nullptr; b.v3_slots = nullptr;
     if ((rc = upload(&b.nrec, nr[k].data(), nr[k].size(), &dummy)) != D4B_OK) return rc;
   }
+  if ((rc = d4b_hp_build(m, D, cand, gen)) != D4B_OK) return rc;
   m->n_generic = (int)gen.size();
   std::sort(gen.begin(), gen.end());
   if ((rc = upload(&m->generic_list, gen.data(), gen.size(), &dummy)) != D4B_OK) return rc;

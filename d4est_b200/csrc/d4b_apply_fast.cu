@@ -472,6 +472,7 @@ int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t
 #undef X
     if (rc != D4B_OK) return rc;
   }
+  { int rch = d4b_launch_hp(m, u, Au, st); if (rch != D4B_OK) return rch; }
   if (m->n_generic > 0) return d4b_launch_generic(m, u, Au, m->generic_list, m->n_generic, st);
   return D4B_OK;
 }

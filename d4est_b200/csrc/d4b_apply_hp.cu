@@ -1,0 +1,619 @@
+/* d4b_apply_hp.cu -- degree-templated SIPG apply for the elements of an hp-adaptive mesh that are NOT
+ * "regular": hanging faces in both roles (I am the coarse side: 4 half-mortars on a face; I am a fine
+ * side: the neighbour's trace is evaluated on my quarter of its face), mixed-p neighbours, mortar
+ * quadrature degree above my own, any inter-tree orientation, local or ghost neighbours, Dirichlet
+ * boundary faces.  One template instance per (N, Nq) of the element itself; the neighbour's degree, the
+ * mortar degree and the child indices are per-record run-time data.
+ *
+ * Reference semantics (same operator, one side at a time, see d4b_apply_generic.cu):
+ *   dGMath/d4est_laplacian_with_opt_flux.c:212-813   slice, reorient, project to mortar, interpolate, 1/2
+ *   dGMath/d4est_laplacian_with_opt_flux_sipg.c:529-958  SIPG flux, Galerkin integral, back-projection, lift
+ *   Mesh/d4est_mortars_with_opt.c:521,561            p-/hp-prolongation to the mortar space and its adjoint
+ *   Quadrature/d4est_quadrature.c:263-375            volume stiffness term
+ *
+ * Mapping: ONE WARP PER ELEMENT, no block barrier anywhere (__syncwarp only), a CTA is just a few
+ * independent warps.  Shared memory per warp is sized for the (N, Nq) bucket, not for the largest
+ * element of the level.
+ *   volume: sum-factorised line tasks as in d4b_apply_fast.cu (1-D tables B = I, C = I D of the element's
+ *     own (N, Nq) are compile-time-indexed __constant__ operands of the DFMAs).
+ *   faces: the warp is split into NG groups of 32/NG lanes; each group takes one half-mortar record per
+ *     round and runs T (face traces of u and du/dn, own side from shared memory, neighbour straight from
+ *     global memory) -> S1 (contraction along face axis a with E_a, E_a D) -> QV (along b: u and the three
+ *     reference derivatives at the mortar points, both sides) -> FLUX -> BACK1/BACK2 (adjoint of S1/QV:
+ *     Galerkin integral + back-projection) -> per-face accumulators Y (lift) and Z (normal-derivative lift).
+ *     E = (child) interpolation to the mortar Gauss points composed with the p-/hp-prolongation, tables
+ *     I[deg][degq_mortar][child] and I D from the global 1-D pool (uniform loads).
+ *   lift: Au = volume + sum_faces lift(Y) + D_n^T lift(Z), one direction at a time (v2's LIFT stage).
+ * Records of one face (the 4 children of a hanging face) and faces that share an edge accumulate in a
+ * fixed group order, so results are bitwise reproducible run to run.
+ */
+#include "d4b_internal.h"
+#include "d4b_ops.h"
+#include <vector>
+#include <cstdlib>
+#include <cstring>
+#include <algorithm>
+
+struct hp_rec {       /* 32 bytes: one half-mortar, resolved once per level */
+  int64_t fac_off;    /* my factor block: a-[3], (a+[3],) sj*sigma, Nm^2 each                           */
+  int64_t g_off;      /* boundary: Dirichlet data or -1                                                */
+  int64_t nbr_u;      /* >= 0 offset into u; < 0: -(offset into u_ghost) - 1                           */
+  int32_t code;       /* bits 0-2 f_m, 3-5 f_p, 6-8 tcode, 9-11 child_m+1, 12-14 child_p+1, 15 boundary */
+  int32_t dims;       /* Nm | Np << 8                                                                  */
+};
+struct hp_slot { int64_t node_off, quad_off; int32_t rec_begin, nrec; int64_t pad; };
+
+__constant__ d4b_ops_dev c_hp_ops[2];
+
+template <int N, int Nq> struct hp_tab { double B[Nq * N], C[Nq * N], D[N * N]; };
+
+/* (N, Nq, NG): NG record groups per warp */
+#define HP_PAIRS(X) X(2, 2, 4) X(2, 3, 4) X(2, 4, 4) X(3, 3, 4) X(3, 4, 4) X(3, 5, 4) X(4, 4, 4) X(4, 5, 4) X(4, 6, 4) \
+                    X(5, 5, 2) X(5, 6, 2) X(5, 7, 2) X(6, 6, 2) X(6, 7, 2) X(6, 8, 2) X(7, 7, 1) X(7, 8, 1) X(7, 9, 1) \
+                    X(8, 8, 1) X(8, 9, 1) X(8, 10, 1)
+#define HP_MAXNP 8     /* neighbour N handled by the templated line tasks */
+#define HP_MAXNM 12
+
+/* one immutable __constant__ table per template instance (written once per quadrature type) */
+template <int N, int Nq> struct hp_const;
+#define X(a, b, g)                                                                                          \
+  __constant__ hp_tab<a, b> c_hp_##a##_##b;                                                                 \
+  template <> struct hp_const<a, b> {                                                                       \
+    static __device__ __forceinline__ const hp_tab<a, b> &get() { return c_hp_##a##_##b; }                  \
+    static cudaError_t put(const hp_tab<a, b> *h) { return cudaMemcpyToSymbol(c_hp_##a##_##b, h, sizeof(*h)); } \
+  };
+HP_PAIRS(X)
+#undef X
+
+struct hp_args {
+  const hp_slot *slots; const hp_rec *recs; const double *G, *fac, *bc_g, *u, *u_ghost; double *Au;
+  int n_list, qt, NMX, MX, per_warp;
+};
+
+template <int N, int Nq> struct HL {
+  static constexpr int N2 = N * N, N3 = N2 * N, Q2 = Nq * Nq, Q3 = Q2 * Nq, NQ = N * Nq;
+  static constexpr int SJ = N + 1, SK = N * (N + 1), UA = N * SK;   /* U, ACC: (i,j,k) -> i + SJ j + SK k */
+  static constexpr int AS = N2 + (N == 4 ? 4 : 0), AB = Nq * AS;     /* A bufs: (i,j,c) -> i + N j + AS c  */
+  static constexpr int BS = NQ + 1, BB = Nq * BS;                    /* B bufs: (i,c,b) -> i + N c + BS b  */
+  static constexpr int VOL = 2 * AB + 3 * BB;
+  static constexpr int FIXED = 2 * UA + 12 * N2;
+};
+__host__ __device__ static inline int hp_group_doubles(int NMX, int MX)
+{ int rb = 6 * NMX * MX > 4 * NMX * NMX ? 6 * NMX * MX : 4 * NMX * NMX; return 8 * NMX * NMX + rb; }
+
+template <int n> __device__ __forceinline__ void hld(const double *p, int st, double (&x)[n])
+{
+#pragma unroll
+  for (int i = 0; i < n; i++) x[i] = p[i * st];
+}
+template <int n> __device__ __forceinline__ void hst(double *p, int s, const double (&x)[n])
+{
+#pragma unroll
+  for (int i = 0; i < n; i++) p[i * s] = x[i];
+}
+/* y[o] = sum_i M(o,i) x[i], M compile-time-indexed (constant-bank operands) */
+template <int NI, int NO, bool TR>
+__device__ __forceinline__ void hmat(const double *M, const double (&x)[NI], double (&y)[NO])
+{
+#pragma unroll
+  for (int o = 0; o < NO; o++) {
+    double s = 0.;
+#pragma unroll
+    for (int i = 0; i < NI; i++) s = fma(TR ? M[i * NO + o] : M[o * NI + i], x[i], s);
+    y[o] = s;
+  }
+}
+template <int NI, int NO, bool TR>
+__device__ __forceinline__ void hmat_acc(const double *M, const double (&x)[NI], double (&y)[NO])
+{
+#pragma unroll
+  for (int o = 0; o < NO; o++) {
+    double s = y[o];
+#pragma unroll
+    for (int i = 0; i < NI; i++) s = fma(TR ? M[i * NO + o] : M[o * NI + i], x[i], s);
+    y[o] = s;
+  }
+}
+/* dot of a run-time table row (global 1-D pool, uniform address inside a record group) with a register line */
+template <int NI> __device__ __forceinline__ double hdot(const double *__restrict__ row, const double (&x)[NI])
+{
+  double m[NI];
+#pragma unroll
+  for (int i = 0; i < NI; i++) m[i] = __ldg(row + i);
+  double s = 0.;
+#pragma unroll
+  for (int i = 0; i < NI; i++) s = fma(m[i], x[i], s);
+  return s;
+}
+
+/* S1: one face line along axis a (u or du/dn at fixed b) -> mortar points along a:
+ *   fld 0: o[q] = E x, o[pl + q] = (E D) x;   fld 1: o[2 pl + q] = E x                                  */
+template <int NP>
+__device__ __forceinline__ void hp_s1_line(const double *in, const double *__restrict__ E, const double *__restrict__ ED,
+                                           int Nm, double *o, int pl, int fld)
+{
+  double x[NP]; hld<NP>(in, 1, x);
+  if (fld == 0) {
+    for (int q = 0; q < Nm; q++) { o[q] = hdot<NP>(E + q * NP, x); o[pl + q] = hdot<NP>(ED + q * NP, x); }
+  } else {
+    for (int q = 0; q < Nm; q++) o[2 * pl + q] = hdot<NP>(E + q * NP, x);
+  }
+}
+/* QV: the three S1 fields at fixed mortar coordinate qa, contracted along b:
+ *   out[0] = u, out[(1+ia) Nm2] = du/d(axis a), out[(1+ib) Nm2] = du/d(axis b), out[(1+dn) Nm2] = du/dn      */
+template <int NP>
+__device__ __forceinline__ void hp_qv_line(const double *in, int Nm, int pl, const double *__restrict__ E,
+                                           const double *__restrict__ ED, double *out, int Nm2, int ia, int ib, int dn)
+{
+  double x1[NP], x2[NP], x3[NP];
+  hld<NP>(in, Nm, x1); hld<NP>(in + pl, Nm, x2); hld<NP>(in + 2 * pl, Nm, x3);
+  for (int qb = 0; qb < Nm; qb++) {
+    double e[NP], ed[NP];
+#pragma unroll
+    for (int i = 0; i < NP; i++) { e[i] = __ldg(E + qb * NP + i); ed[i] = __ldg(ED + qb * NP + i); }
+    double su = 0., sa = 0., sb = 0., sn = 0.;
+#pragma unroll
+    for (int i = 0; i < NP; i++) {
+      su = fma(e[i], x1[i], su); sa = fma(e[i], x2[i], sa); sb = fma(ed[i], x1[i], sb); sn = fma(e[i], x3[i], sn);
+    }
+    double *o = out + Nm * qb;
+    o[0] = su; o[(1 + ia) * Nm2] = sa; o[(1 + ib) * Nm2] = sb; o[(1 + dn) * Nm2] = sn;
+  }
+}
+#define HP_NP_SWITCH(np, CALL)                                                                      \
+  switch (np) {                                                                                     \
+    case 2: { constexpr int NP = 2; CALL; } break; case 3: { constexpr int NP = 3; CALL; } break;   \
+    case 4: { constexpr int NP = 4; CALL; } break; case 5: { constexpr int NP = 5; CALL; } break;   \
+    case 6: { constexpr int NP = 6; CALL; } break; case 7: { constexpr int NP = 7; CALL; } break;   \
+    default: { constexpr int NP = 8; CALL; } break;                                                 \
+  }
+
+__device__ __forceinline__ void hp_face_strides(int d, int sj, int sk, int &sa, int &sb, int &sn)
+{
+  sa = d == 0 ? sj : 1; sb = d == 2 ? sj : sk; sn = d == 0 ? 1 : (d == 1 ? sj : sk);
+}
+__device__ __forceinline__ int hp_tcode_src(int tcode, int n, int a, int b)
+{ /* m-order point -> p-order point (d4b_hm_t.tcode) */
+  int x = (tcode & 1) ? a : b, y = (tcode & 1) ? b : a;
+  if (tcode & 2) x = n - 1 - x;
+  if (tcode & 4) y = n - 1 - y;
+  return x + n * y;
+}
+
+template <int N, int Nq, int NG>
+__global__ void __launch_bounds__(128) d4b_apply_hp_kernel(const hp_args A)
+{
+  using L = HL<N, Nq>;
+  constexpr int N2 = L::N2, N3 = L::N3, Q2 = L::Q2, Q3 = L::Q3, NQ = L::NQ;
+  constexpr int SJ = L::SJ, SK = L::SK, AS = L::AS, BS = L::BS;
+  constexpr int GS = 32 / NG;
+  extern __shared__ double sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slot = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (slot >= A.n_list) return;                         /* warps are independent: no block barrier below */
+  const hp_tab<N, Nq> &T = hp_const<N, Nq>::get();
+  const double *B = T.B, *C = T.C, *D = T.D;
+  double *U = sm + (size_t)warp * A.per_warp, *ACC = U + L::UA, *YZ = ACC + L::UA, *S = YZ + 12 * N2;
+  const hp_slot sl = A.slots[slot];
+  const double *ue = A.u + sl.node_off;
+
+  { /* L2 prefetch of what is read once, later: the metric block and the factor blocks of the records */
+    const char *g = reinterpret_cast<const char *>(A.G + 6 * sl.quad_off);
+    for (int o = lane * 128; o < 6 * Q3 * 8; o += 32 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
+    for (int r = lane >> 2; r < sl.nrec; r += 8) {
+      const hp_rec *h = A.recs + sl.rec_begin + r;
+      const int nm = __ldg(&h->dims) & 255, bytes = ((__ldg(&h->code) >> 15) & 1 ? 4 : 7) * nm * nm * 8;
+      const char *p = reinterpret_cast<const char *>(A.fac + __ldg(&h->fac_off));
+      for (int o = (lane & 3) * 128; o < bytes; o += 4 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+    }
+  }
+  for (int i = lane; i < N3; i += 32) U[(i % N) + SJ * ((i / N) % N) + SK * (i / N2)] = ue[i];
+  for (int i = lane; i < 12 * N2; i += 32) YZ[i] = 0.;
+  __syncwarp();
+
+  /* ---------------- volume (Quadrature/d4est_quadrature.c:263-375, sum-factorised) */
+  {
+    double *V0 = S, *V1 = S + L::AB, *V2 = S + 2 * L::AB, *V3 = V2 + L::BB, *V4 = V3 + L::BB;
+    for (int t = lane; t < N2; t += 32) { /* along t: line (i,j) */
+      const int i = t % N, j = t / N;
+      double x[N], y[Nq];
+      hld<N>(U + i + SJ * j, SK, x);
+      hmat<N, Nq, false>(B, x, y); hst<Nq>(V0 + t, AS, y);
+      hmat<N, Nq, false>(C, x, y); hst<Nq>(V1 + t, AS, y);
+    }
+    __syncwarp();
+    for (int t = lane; t < NQ; t += 32) { /* along s: lines (i,c) */
+      const int i = t % N, c = t / N;
+      double x[N], y[Nq];
+      hld<N>(V0 + i + AS * c, N, x);
+      hmat<N, Nq, false>(B, x, y); hst<Nq>(V2 + i + N * c, BS, y);
+      hmat<N, Nq, false>(C, x, y); hst<Nq>(V3 + i + N * c, BS, y);
+      hld<N>(V1 + i + AS * c, N, x);
+      hmat<N, Nq, false>(B, x, y); hst<Nq>(V4 + i + N * c, BS, y);
+    }
+    __syncwarp();
+    const double *Ge = A.G + 6 * sl.quad_off;
+    for (int t = lane; t < Q2; t += 32) { /* along r: lines (b,c); metric; transposed r-contraction in registers */
+      const int b = t % Nq, c = t / Nq;
+      double Gv[6][Nq];
+#pragma unroll
+      for (int k = 0; k < 6; k++)
+#pragma unroll
+        for (int a = 0; a < Nq; a++) Gv[k][a] = __ldg(Ge + k * Q3 + Nq * t + a);
+      double x[N], gr[Nq], gs[Nq], gt[Nq];
+      const int o = BS * b + N * c;
+      hld<N>(V2 + o, 1, x); hmat<N, Nq, false>(C, x, gr);
+      hld<N>(V3 + o, 1, x); hmat<N, Nq, false>(B, x, gs);
+      hld<N>(V4 + o, 1, x); hmat<N, Nq, false>(B, x, gt);
+#pragma unroll
+      for (int a = 0; a < Nq; a++) {
+        const double g0 = gr[a], g1 = gs[a], g2 = gt[a];
+        gr[a] = Gv[0][a] * g0 + Gv[1][a] * g1 + Gv[2][a] * g2;
+        gs[a] = Gv[1][a] * g0 + Gv[3][a] * g1 + Gv[4][a] * g2;
+        gt[a] = Gv[2][a] * g0 + Gv[4][a] * g1 + Gv[5][a] * g2;
+      }
+      hmat<Nq, N, true>(C, gr, x); hst<N>(V2 + o, 1, x);
+      hmat<Nq, N, true>(B, gs, x); hst<N>(V3 + o, 1, x);
+      hmat<Nq, N, true>(B, gt, x); hst<N>(V4 + o, 1, x);
+    }
+    __syncwarp();
+    for (int t = lane; t < NQ; t += 32) { /* transposed s-contraction: lines (i,c) */
+      const int i = t % N, c = t / N;
+      double x[Nq], y[N];
+      hld<Nq>(V2 + i + N * c, BS, x); hmat<Nq, N, true>(B, x, y);
+      hld<Nq>(V3 + i + N * c, BS, x); hmat_acc<Nq, N, true>(C, x, y);
+      hst<N>(V0 + i + AS * c, N, y);
+      hld<Nq>(V4 + i + N * c, BS, x); hmat<Nq, N, true>(B, x, y);
+      hst<N>(V1 + i + AS * c, N, y);
+    }
+    __syncwarp();
+    for (int t = lane; t < N2; t += 32) { /* transposed t-contraction: line (i,j) -> ACC */
+      const int i = t % N, j = t / N;
+      double x[Nq], y[N];
+      hld<Nq>(V0 + t, AS, x); hmat<Nq, N, true>(B, x, y);
+      hld<Nq>(V1 + t, AS, x); hmat_acc<Nq, N, true>(C, x, y);
+      hst<N>(ACC + i + SJ * j, SK, y);
+    }
+    __syncwarp();
+  }
+
+  /* ---------------- faces: NG half-mortar records per round, one per group of GS lanes */
+  const int MX = A.MX, M2 = MX * MX;
+  const int g = lane / GS, gl = lane % GS;
+  double *RA = S + g * hp_group_doubles(A.NMX, MX), *RB = RA + 8 * A.NMX * A.NMX;
+  const d4b_ops_dev &ops = c_hp_ops[A.qt];
+  const double *pool = ops.pool;
+#pragma unroll 1
+  for (int r0 = 0; r0 < sl.nrec; r0 += NG) {
+    const bool on = r0 + g < sl.nrec;
+    hp_rec R; R.fac_off = 0; R.g_off = -1; R.nbr_u = 0; R.code = 0; R.dims = (N << 8) | Nq;
+    if (on) R = A.recs[sl.rec_begin + r0 + g];
+    const int fm = R.code & 7, fp = (R.code >> 3) & 7, tc = (R.code >> 6) & 7;
+    const int cm = ((R.code >> 9) & 7) - 1, cp = ((R.code >> 12) & 7) - 1;
+    const bool bnd = (R.code >> 15) & 1;
+    const int Nm = R.dims & 255, Np = (R.dims >> 8) & 255, Nm2 = Nm * Nm, mdq = Nm - 1;
+    const int d = fm >> 1, ia = d == 0 ? 1 : 0, ib = d == 2 ? 1 : 2;
+    const int dp = fp >> 1, iap = dp == 0 ? 1 : 0, ibp = dp == 2 ? 1 : 2;
+    const int ca = cm < 0 ? 0 : 1 + (cm & 1), cb = cm < 0 ? 0 : 1 + ((cm >> 1) & 1);
+    const int cpa = cp < 0 ? 0 : 1 + (cp & 1), cpb = cp < 0 ? 0 : 1 + ((cp >> 1) & 1);
+    const double *Ea = pool + ops.idx.I[N - 1][mdq][ca], *EaD = pool + ops.idx.ID[N - 1][mdq][ca];
+    const double *Eb = pool + ops.idx.I[N - 1][mdq][cb], *EbD = pool + ops.idx.ID[N - 1][mdq][cb];
+    const double *Pa = pool + ops.idx.I[Np - 1][mdq][cpa], *PaD = pool + ops.idx.ID[Np - 1][mdq][cpa];
+    const double *Pb = pool + ops.idx.I[Np - 1][mdq][cpb], *PbD = pool + ops.idx.ID[Np - 1][mdq][cpb];
+    const double *F = A.fac + R.fac_off;
+    const int pl = Nm * MX;   /* plane stride of the S1 buffers */
+
+    /* T: traces at face nodes.  RA[0 + t] = u-, RA[M2 + t] = du-/dn, RA[2 M2 + t'] = u+, RA[3 M2 + t'] = du+/dn */
+    if (on) {
+      int sa, sb, sn; hp_face_strides(d, SJ, SK, sa, sb, sn);
+      const int lay = (fm & 1) ? N - 1 : 0;
+      const int Np2 = Np * Np, ntask = N2 + (bnd ? 0 : Np2);
+      const double *un = bnd ? nullptr : (R.nbr_u >= 0 ? A.u + R.nbr_u : A.u_ghost + (-R.nbr_u - 1));
+      const int pa = dp == 0 ? Np : 1, pb = dp == 2 ? Np : Np2, pn = dp == 0 ? 1 : (dp == 1 ? Np : Np2);
+      const int layp = (fp & 1) ? Np - 1 : 0;
+      const double *Dp = pool + ops.idx.D[Np - 1] + layp * Np;
+      for (int t = gl; t < ntask; t += GS) {
+        if (t < N2) {
+          const int a = t % N, b = t / N;
+          double x[N]; hld<N>(U + a * sa + b * sb, sn, x);
+          double dn = 0.;
+#pragma unroll
+          for (int m = 0; m < N; m++) dn = fma(D[lay * N + m], x[m], dn);
+          RA[t] = (fm & 1) ? x[N - 1] : x[0];
+          RA[M2 + t] = dn;
+        } else {
+          const int tt = t - N2, a = tt % Np, b = tt / Np;
+          const double *p = un + a * pa + b * pb;
+          double dn = 0., ul = 0.;
+          for (int m = 0; m < Np; m++) {
+            const double v = __ldg(p + m * pn);
+            dn = fma(__ldg(Dp + m), v, dn);
+            if (m == layp) ul = v;
+          }
+          RA[2 * M2 + tt] = ul; RA[3 * M2 + tt] = dn;
+        }
+      }
+    }
+    __syncwarp();
+    /* S1: along face axis a.  RB[(3 side + k) pl + q + Nm b], k = {E u, E D u, E dn} */
+    if (on) {
+      const int ntask = 2 * N + (bnd ? 0 : 2 * Np);
+      for (int t = gl; t < ntask; t += GS) {
+        if (t < 2 * N) {
+          const int fld = t / N, b = t % N;
+          hp_s1_line<N>(RA + fld * M2 + N * b, Ea, EaD, Nm, RB + Nm * b, pl, fld);
+        } else {
+          const int tt = t - 2 * N, fld = tt / Np, b = tt % Np;
+          HP_NP_SWITCH(Np, hp_s1_line<NP>(RA + (2 + fld) * M2 + Np * b, Pa, PaD, Nm, RB + 3 * pl + Nm * b, pl, fld))
+        }
+      }
+    }
+    __syncwarp();
+    /* QV: along face axis b.  RA[(4 side + fld) Nm2 + q], fld 0 = u, 1 + l = du/dr_l (l in that side's frame) */
+    if (on) {
+      const int ntask = bnd ? Nm : 2 * Nm;
+      for (int t = gl; t < ntask; t += GS) {
+        if (t < Nm) {
+          hp_qv_line<N>(RB + t, Nm, pl, Eb, EbD, RA + t, Nm2, ia, ib, d);
+        } else {
+          const int qa = t - Nm;
+          HP_NP_SWITCH(Np, hp_qv_line<NP>(RB + 3 * pl + qa, Nm, pl, Pb, PbD, RA + 4 * Nm2 + qa, Nm2, iap, ibp, dp))
+        }
+      }
+    }
+    __syncwarp();
+    /* FLUX at the mortar quadrature points (..._flux_sipg.c:645-677 interior, :139-191 Dirichlet):
+     * RB[k Nm2 + q], k = 0: tested with v; 1, 2: tested with dv/d(axis a), dv/d(axis b); 3: with dv/dn */
+    if (on) {
+      const double *wq = pool + ops.idx.w[mdq];
+      for (int q = gl; q < Nm2; q += GS) {
+        const int a = q % Nm, b = q / Nm;
+        const double w = __ldg(wq + a) * __ldg(wq + b);
+        const double am0 = __ldg(F + q), am1 = __ldg(F + Nm2 + q), am2 = __ldg(F + 2 * Nm2 + q);
+        const double um = RA[q];
+        const double qm = am0 * RA[Nm2 + q] + am1 * RA[2 * Nm2 + q] + am2 * RA[3 * Nm2 + q];
+        double jump, t1, sjs, hs;
+        if (!bnd) {
+          const int s = hp_tcode_src(tc, Nm, a, b);
+          const double qp = __ldg(F + 3 * Nm2 + q) * RA[5 * Nm2 + s] + __ldg(F + 4 * Nm2 + q) * RA[6 * Nm2 + s] +
+                            __ldg(F + 5 * Nm2 + q) * RA[7 * Nm2 + s];
+          jump = um - RA[4 * Nm2 + s]; t1 = -0.5 * (qm + qp); sjs = __ldg(F + 6 * Nm2 + q); hs = -0.5;
+        } else {
+          const double gv = R.g_off >= 0 ? __ldg(A.bc_g + R.g_off + q) : 0.;
+          jump = um - gv; t1 = -qm; sjs = __ldg(F + 3 * Nm2 + q); hs = -1.0;
+        }
+        const double wj = w * hs * jump;
+        RB[q] = w * (t1 + sjs * jump);
+        RB[Nm2 + q] = wj * (d == 0 ? am1 : am0);
+        RB[2 * Nm2 + q] = wj * (d == 2 ? am1 : am2);
+        RB[3 * Nm2 + q] = wj * (d == 0 ? am0 : (d == 1 ? am1 : am2));
+      }
+    }
+    __syncwarp();
+    /* BACK1: adjoint of QV along b.  RA[k NmN + qa + Nm j], k = 0: Eb^T F + (Eb D)^T Hb, 1: Eb^T Ha, 2: Eb^T Hn */
+    const int NmN = Nm * N;
+    if (on) {
+      for (int t = gl; t < 3 * Nm; t += GS) {
+        const int k = t / Nm, qa = t % Nm;
+        double y[N];
+#pragma unroll
+        for (int j = 0; j < N; j++) y[j] = 0.;
+        const double *f0 = RB + (k == 0 ? 0 : (k == 1 ? Nm2 : 3 * Nm2)) + qa;
+        for (int qb = 0; qb < Nm; qb++) {
+          const double v = f0[Nm * qb];
+#pragma unroll
+          for (int j = 0; j < N; j++) y[j] = fma(__ldg(Eb + qb * N + j), v, y[j]);
+          if (k == 0) {
+            const double v2 = RB[2 * Nm2 + qa + Nm * qb];
+#pragma unroll
+            for (int j = 0; j < N; j++) y[j] = fma(__ldg(EbD + qb * N + j), v2, y[j]);
+          }
+        }
+        hst<N>(RA + k * NmN + qa, Nm, y);
+      }
+    }
+    __syncwarp();
+    /* BACK2: adjoint of S1 along a.  RB[k N2 + a' + N b'], k = 0: Y (lifted onto the face layer), 1: Z (normal lift) */
+    if (on) {
+      for (int t = gl; t < 2 * N; t += GS) {
+        const int k = t / N, bp = t % N;
+        double y[N];
+#pragma unroll
+        for (int j = 0; j < N; j++) y[j] = 0.;
+        const double *x1 = RA + (k == 0 ? 0 : 2 * NmN) + Nm * bp;
+        for (int qa = 0; qa < Nm; qa++) {
+          const double v = x1[qa];
+#pragma unroll
+          for (int j = 0; j < N; j++) y[j] = fma(__ldg(Ea + qa * N + j), v, y[j]);
+          if (k == 0) {
+            const double v2 = RA[NmN + Nm * bp + qa];
+#pragma unroll
+            for (int j = 0; j < N; j++) y[j] = fma(__ldg(EaD + qa * N + j), v2, y[j]);
+          }
+        }
+        hst<N>(RB + k * N2 + N * bp, 1, y);
+      }
+    }
+    __syncwarp();
+    /* accumulate per face, groups in fixed order (children of one face share Y, Z) */
+#pragma unroll
+    for (int gg = 0; gg < NG; gg++) {
+      if (g == gg && on)
+        for (int t = gl; t < 2 * N2; t += GS) YZ[fm * 2 * N2 + t] += RB[t];
+      __syncwarp();
+    }
+  }
+
+  /* ---------------- LIFT (..._flux_sipg.c:918-958): face layer += Y, normal line += D[layer,:] Z; then store */
+#pragma unroll 1
+  for (int d = 0; d < 3; d++) {
+    int sa, sb, sn; hp_face_strides(d, SJ, SK, sa, sb, sn);
+    for (int t = lane; t < N2; t += 32) {
+      double *acc = ACC + (t % N) * sa + (t / N) * sb;
+      const double y0 = YZ[(4 * d) * N2 + t], z0 = YZ[(4 * d + 1) * N2 + t];
+      const double y1 = YZ[(4 * d + 2) * N2 + t], z1 = YZ[(4 * d + 3) * N2 + t];
+#pragma unroll
+      for (int m = 0; m < N; m++) {
+        double v = acc[m * sn] + D[m] * z0 + D[(N - 1) * N + m] * z1;
+        if (m == 0) v += y0;
+        if (m == N - 1) v += y1;
+        acc[m * sn] = v;
+      }
+    }
+    __syncwarp();
+  }
+  double *Aue = A.Au + sl.node_off;
+  for (int i = lane; i < N3; i += 32) Aue[i] = ACC[(i % N) + SJ * ((i / N) % N) + SK * (i / N2)];
+}
+
+/* ------------------------------------------------------------------ host side */
+struct hp_bucket_host { std::vector<hp_slot> slots; std::vector<hp_rec> recs; int NMX = 0, MX = 0; };
+
+bool d4b_hp_supported(int N, int Nq)
+{
+#define X(a, b, g) if (N == a && Nq == b) return true;
+  HP_PAIRS(X)
+#undef X
+  return false;
+}
+
+template <int N, int Nq> static size_t hp_warp_doubles(int NMX, int MX, int NG)
+{
+  using L = HL<N, Nq>;
+  int scr = NG * hp_group_doubles(NMX, MX);
+  if (scr < L::VOL) scr = L::VOL;
+  return (size_t)L::FIXED + scr;
+}
+static size_t hp_warp_doubles_rt(int N, int Nq, int NMX, int MX)
+{
+#define X(a, b, g) if (N == a && Nq == b) return hp_warp_doubles<a, b>(NMX, MX, g);
+  HP_PAIRS(X)
+#undef X
+  return (size_t)1 << 40;
+}
+
+/* Take the elements of `cand` the templated hp kernel can run (instance exists, neighbour N <= HP_MAXNP,
+ * mortar points <= HP_MAXNM, one warp's scratch fits) into (N, Nq) buckets with resolved per-record
+ * metadata; the others are appended to `rest` (completeness kernel). */
+int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_t> &cand, std::vector<int32_t> &rest)
+{
+  m->n_hp = 0;
+  if (!D->hm) { rest.insert(rest.end(), cand.begin(), cand.end()); return D4B_OK; }
+  std::vector<hp_bucket_host> hb(D4B_NDEG * D4B_NDEGQ);
+  const int nl = m->n_local;
+  for (int32_t e : cand) {
+    const int N = D->deg[e] + 1, Nq = D->degq[e] + 1;
+    bool ok = d4b_hp_supported(N, Nq);
+    int nmx = Nq, mx = N;
+    for (int r = D->hm_begin[e]; ok && r < D->hm_begin[e + 1]; r++) {
+      const d4b_hm_t &h = D->hm[r];
+      const int Nm = h.degq + 1;
+      if (Nm > HP_MAXNM || Nm < N) ok = false;
+      if (h.nbr >= 0) { const int Np = D->deg[h.nbr] + 1; if (Np > HP_MAXNP || Np > Nm) ok = false; if (Np > mx) mx = Np; }
+      if (Nm > nmx) nmx = Nm;
+    }
+    if (ok && hp_warp_doubles_rt(N, Nq, nmx, mx) * 8 > 200 * 1024) ok = false;
+    if (!ok) { rest.push_back(e); continue; }
+    hp_bucket_host &b = hb[(N - 1) * D4B_NDEGQ + (Nq - 1)];
+    hp_slot s; s.node_off = D->node_off[e]; s.quad_off = D->quad_off[e];
+    s.rec_begin = (int32_t)b.recs.size(); s.nrec = D->hm_begin[e + 1] - D->hm_begin[e]; s.pad = 0;
+    for (int r = D->hm_begin[e]; r < D->hm_begin[e + 1]; r++) {
+      const d4b_hm_t &h = D->hm[r];
+      hp_rec R; R.fac_off = h.fac_off; R.g_off = h.g_off; R.nbr_u = 0;
+      const int bnd = h.nbr < 0;
+      int Np = N;
+      if (!bnd) {
+        Np = D->deg[h.nbr] + 1;
+        R.nbr_u = h.nbr < nl ? D->node_off[h.nbr] : -(D->node_off[h.nbr] - D->node_off[nl]) - 1;
+      }
+      R.code = (h.f_m & 7) | (((bnd ? 0 : h.f_p) & 7) << 3) | ((h.tcode & 7) << 6) | ((h.child_m + 1) << 9) |
+               (((bnd ? -1 : h.child_p) + 1) << 12) | (bnd << 15);
+      R.dims = (h.degq + 1) | (Np << 8);
+      b.recs.push_back(R);
+    }
+    b.slots.push_back(s);
+    if (nmx > b.NMX) b.NMX = nmx;
+    if (mx > b.MX) b.MX = mx;
+  }
+  for (int k = 0; k < D4B_NDEG * D4B_NDEGQ; k++) {
+    hp_bucket_host &b = hb[k];
+    if (b.slots.empty()) continue;
+    if (m->n_hp == D4B_MAX_BUCKETS) { d4b_set_error("more than %d (deg, deg_quad) pairs on one level", D4B_MAX_BUCKETS); return D4B_EINVAL; }
+    d4b_hp_bucket &o = m->hp[m->n_hp++];
+    o.N = k / D4B_NDEGQ + 1; o.Nq = k % D4B_NDEGQ + 1; o.count = (int)b.slots.size(); o.NMX = b.NMX; o.MX = b.MX;
+    o.n_rec = (int)b.recs.size();
+    D4B_CUDA(cudaMalloc(&o.slots, b.slots.size() * sizeof(hp_slot)));
+    D4B_CUDA(cudaMemcpy(o.slots, b.slots.data(), b.slots.size() * sizeof(hp_slot), cudaMemcpyHostToDevice));
+    D4B_CUDA(cudaMalloc(&o.recs, b.recs.size() * sizeof(hp_rec)));
+    D4B_CUDA(cudaMemcpy(o.recs, b.recs.data(), b.recs.size() * sizeof(hp_rec), cudaMemcpyHostToDevice));
+  }
+  return D4B_OK;
+}
+
+static int hp_bind_ops(int qt)
+{
+  static bool bound[2] = {false, false};
+  if (bound[qt]) return D4B_OK;
+  const d4b_ops_dev *ops = d4b_ops_device(qt);
+  if (!ops) return D4B_ECUDA;
+  D4B_CUDA(cudaMemcpyToSymbol(c_hp_ops, ops, sizeof(d4b_ops_dev), qt * sizeof(d4b_ops_dev), cudaMemcpyHostToDevice));
+  bound[qt] = true;
+  return D4B_OK;
+}
+
+template <int N, int Nq, int NG>
+static int hp_launch_bucket(const d4b_mesh *m, const d4b_hp_bucket &b, const double *u, double *Au, cudaStream_t st)
+{
+  /* the element's own tables live in a __constant__ block of this instance: written once; a level with the
+   * other quadrature type waits for everything in flight before it is replaced */
+  static int have_qt = -1;
+  static size_t attr_smem = 0;
+  if (have_qt != m->quad_type) {
+    if (have_qt != -1) D4B_CUDA(cudaDeviceSynchronize());
+    hp_tab<N, Nq> t;
+    double I[D4B_OPS_MAXN * D4B_OPS_MAXN], Dm[D4B_OPS_MAXN * D4B_OPS_MAXN];
+    d4b_ops_interp(N - 1, Nq - 1, m->quad_type, -1, I); d4b_ops_diff(N - 1, Dm);
+    for (int q = 0; q < Nq; q++)
+      for (int j = 0; j < N; j++) {
+        t.B[q * N + j] = I[q * N + j];
+        double s = 0.;
+        for (int k = 0; k < N; k++) s += I[q * N + k] * Dm[k * N + j];
+        t.C[q * N + j] = s;
+      }
+    for (int i = 0; i < N * N; i++) t.D[i] = Dm[i];
+    D4B_CUDA((hp_const<N, Nq>::put(&t)));
+    have_qt = m->quad_type;
+  }
+  const size_t per_warp = hp_warp_doubles<N, Nq>(b.NMX, b.MX, NG);
+  int wpb = 4;
+  while (wpb > 1 && wpb * per_warp * 8 > 110 * 1024) wpb >>= 1;   /* two CTAs per SM where it fits */
+  const size_t smem = wpb * per_warp * 8;
+  if (smem > attr_smem) {
+    D4B_CUDA(cudaFuncSetAttribute(d4b_apply_hp_kernel<N, Nq, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_smem = smem;
+  }
+  hp_args A;
+  A.slots = (const hp_slot *)b.slots; A.recs = (const hp_rec *)b.recs; A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
+  A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.n_list = b.count; A.qt = m->quad_type; A.NMX = b.NMX; A.MX = b.MX;
+  A.per_warp = (int)per_warp;
+  d4b_apply_hp_kernel<N, Nq, NG><<<(b.count + wpb - 1) / wpb, 32 * wpb, smem, st>>>(A);
+  D4B_CUDA(cudaGetLastError());
+  d4b_count_launch(1);
+  return D4B_OK;
+}
+
+int d4b_launch_hp(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st)
+{
+  if (m->n_hp == 0) return D4B_OK;
+  int rc = hp_bind_ops(m->quad_type);
+  if (rc != D4B_OK) return rc;
+  for (int i = 0; i < m->n_hp; i++) {
+    const d4b_hp_bucket &b = m->hp[i];
+    rc = D4B_EINVAL;
+#define X(a, c, g) if (b.N == a && b.Nq == c) rc = hp_launch_bucket<a, c, g>(m, b, u, Au, st);
+    HP_PAIRS(X)
+#undef X
+    if (rc != D4B_OK) return rc;
+  }
+  return D4B_OK;
+}

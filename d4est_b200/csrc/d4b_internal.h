@@ -14,6 +14,7 @@ struct d4b_ops_index {
   int w[D4B_NDEGQ];                /* Nq quadrature weights                              */
   int I[D4B_NDEG][D4B_NDEGQ][3];   /* Nq x N interpolation GLL->quad; [0] full face,
                                       [1] child 0 (lower half), [2] child 1 (upper half) */
+  int ID[D4B_NDEG][D4B_NDEGQ][3];  /* I D: reference derivative evaluated at the same points     */
 };
 
 struct d4b_ops_dev {
@@ -30,7 +31,12 @@ struct d4b_fast_bucket {
   int32_t *nrec;        /* device: [count][6] record of the NEIGHBOUR for the same face (its a- is my
                            -a+), -1 boundary, -2 none (ghost / not mirrored: use my own a+)   */
 };
-#define D4B_MAX_BUCKETS 32
+#define D4B_MAX_BUCKETS 48
+/* one (N, Nq) bucket of the templated hanging / mixed-p kernel (d4b_apply_hp.cu) */
+struct d4b_hp_bucket {
+  int N, Nq, count, n_rec, NMX, MX;   /* NMX: largest mortar Nm, MX: largest of N and the neighbours' N */
+  void *slots, *recs;                 /* device: hp_slot[count], hp_rec[n_rec]                          */
+};
 
 /* device-resident mesh level */
 struct d4b_mesh {
@@ -50,6 +56,7 @@ struct d4b_mesh {
   int pipe_ranges, pipe_b[D4B_PIPE_MAX + 1], pipe_need[D4B_PIPE_MAX];   /* range k = slots [pipe_b[k], pipe_b[k+1]) */
   d4b_fast_bucket pipe_late;       /* elements with a face neighbour more than one chunk ahead: computed after the last upload */
   d4b_fast_bucket fast[D4B_MAX_BUCKETS]; int n_fast;
+  d4b_hp_bucket hp[D4B_MAX_BUCKETS]; int n_hp;
   int32_t *generic_list; int n_generic;   /* elements left to the generic kernel */
 };
 
@@ -75,6 +82,8 @@ void d4b_set_error(const char *fmt, ...);
 const d4b_ops_dev *d4b_ops_device(int quad_type); /* lazily built + uploaded */
 void d4b_count_launch(int n);
 bool d4b_fast_supported(int N, int Nq);
+bool d4b_hp_supported(int N, int Nq);
+int d4b_launch_hp(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st);
 bool d4b_v3_supported(int N, int Nq);
 int d4b_launch_v3(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st);
 int d4b_launch_v3_range(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st,

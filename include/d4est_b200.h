@@ -141,6 +141,9 @@ int d4b_apply_dev(d4b_mesh_t *m, const double *u_dev, double *Au_dev, void *cuda
 /* ghost values supplied by the caller (single-process tests of the N>1 layout) */
 int d4b_set_ghost_host(d4b_mesh_t *m, const double *ughost_host);
 int64_t d4b_kernel_launches(void);   /* number of d4b kernels launched so far          */
+/* how the local elements of a level are split over the element kernels: counts[0] register-blocked /
+ * line-task kernels (regular elements), [1] templated hanging / mixed-p kernel, [2] completeness kernel */
+int d4b_mesh_kernel_split(const d4b_mesh_t *m, int64_t counts[3]);
 
 /* ---- rank boundary (one p4est rank = one GPU): replaces d4est_ghost_data_exchange
  *      (Mesh/d4est_ghost_data.c:143-255) and sc_allreduce (Solver/d4est_solver_cg.c:139,165) by

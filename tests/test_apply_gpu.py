@@ -35,6 +35,34 @@ def test_apply_matches_reference(path):
     lvl.close()
 
 
+@pytest.mark.parametrize("path", all_fixtures(), ids=lambda p: os.path.basename(p)[:-4])
+def test_hp_kernel_matches_reference_on_every_element_class(path):
+    """The templated hanging / mixed-p kernel (d4b_apply_hp.cu) run on EVERY element of every fixture
+    (D4B_ALL_HP=1: regular, mixed-p, hanging in both roles, boundary), and the default split (regular elements in
+    the register-blocked / line-task kernels, the others in the hp kernel) against the completeness kernel."""
+    fx = fixture.load(path)
+    out, split = {}, {}
+    for key, env in (("default", {}), ("all_hp", {"D4B_ALL_HP": "1"}), ("no_hp", {"D4B_NO_HP": "1"})):
+        os.environ.update(env)
+        try:
+            lvl = d4est_b200.MeshLevel(fx)
+            split[key] = lvl.kernel_split
+            out[key] = lvl.apply_host(fx["u"])
+            if key == "all_hp":
+                assert np.array_equal(out[key], lvl.apply_host(fx["u"]))   # fixed accumulation order
+            lvl.close()
+        finally:
+            for k in env:
+                del os.environ[k]
+    nl = int(fx["hdr"][0])
+    assert split["all_hp"][0] == 0 and split["no_hp"][1] == 0
+    assert split["all_hp"][1] == nl, split        # every (N, Nq) of the fixtures has an instance
+    assert split["default"][2] == 0, split        # nothing is left to the completeness kernel
+    for key in out:
+        assert rel(out[key], fx["Au_ref_with_opt"]) < TOL, (key, split[key])
+    assert rel(out["all_hp"], out["no_hp"]) < 1e-13
+
+
 @pytest.mark.parametrize("name", ["brick_p3_l2", "cubed_sphere_hp1"])
 def test_apply_matches_oracle_random_input(golden_dir, name):
     fx = fixture.load(os.path.join(golden_dir, name + ".fix"))

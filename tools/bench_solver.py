@@ -82,6 +82,7 @@ def hp_apply(path):
                       "deg_min": int(deg.min()), "deg_max": int(deg.max()), "ms_per_apply": ms,
                       "gdof_per_s": n / ms / 1e6, "algorithmic_GBps": lvl.algorithmic_bytes / ms / 1e6,
                       "hanging_records": int((fx["hm"]["child_m"] >= 0).sum() + (fx["hm"]["child_p"] >= 0).sum()),
+                      "kernel_split_regular_hp_generic": lvl.kernel_split,
                       "rel_l2_vs_reference_Au": parity}), flush=True)
 
 
