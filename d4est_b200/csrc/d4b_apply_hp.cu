@@ -16,16 +16,16 @@
  * element of the level.
  *   volume: sum-factorised line tasks as in d4b_apply_fast.cu (1-D tables B = I, C = I D of the element's
  *     own (N, Nq) are compile-time-indexed __constant__ operands of the DFMAs).
- *   faces: the warp is split into NG groups of 32/NG lanes; each group takes one half-mortar record per
- *     round and runs T (face traces of u and du/dn, own side from shared memory, neighbour straight from
- *     global memory) -> S1 (contraction along face axis a with E_a, E_a D) -> QV (along b: u and the three
- *     reference derivatives at the mortar points, both sides) -> FLUX -> BACK1/BACK2 (adjoint of S1/QV:
- *     Galerkin integral + back-projection) -> per-face accumulators Y (lift) and Z (normal-derivative lift).
- *     E = (child) interpolation to the mortar Gauss points composed with the p-/hp-prolongation, tables
- *     I[deg][degq_mortar][child] and I D from the global 1-D pool (uniform loads).
+ *   faces: one half-mortar record at a time, all 32 lanes: T (face traces of u and du/dn, own side from shared
+ *     memory, neighbour straight from global memory) -> S1 (contraction along face axis a with E_a, E_a D) ->
+ *     QV (along b: u and sum_l a_l du/dr_l at the mortar points, both sides, in my point order) -> FLUX ->
+ *     BACK1/BACK2 (adjoint of QV/S1: Galerkin integral + back-projection) -> per-face accumulators Y (lift) and
+ *     Z (normal-derivative lift).  The contractions are output-stationary: a lane owns one table row (own side
+ *     in registers, N being a template parameter) and sweeps the lines, which arrive as shared-memory
+ *     broadcasts.  E = (child) interpolation to the mortar Gauss points composed with the p-/hp-prolongation,
+ *     tables I[deg][degq_mortar][child] and I D from the global 1-D pool (L1-resident).
  *   lift: Au = volume + sum_faces lift(Y) + D_n^T lift(Z), one direction at a time (v2's LIFT stage).
- * Records of one face (the 4 children of a hanging face) and faces that share an edge accumulate in a
- * fixed group order, so results are bitwise reproducible run to run.
+ * Records are processed in their stored order, so results are bitwise reproducible run to run.
  */
 #include "d4b_internal.h"
 #include "d4b_ops.h"
@@ -47,7 +47,7 @@ __constant__ d4b_ops_dev c_hp_ops[2];
 
 template <int N, int Nq> struct hp_tab { double B[Nq * N], C[Nq * N], D[N * N]; };
 
-/* (N, Nq, NG): NG record groups per warp */
+/* (N, Nq, spare) */
 #define HP_PAIRS(X) X(2, 2, 4) X(2, 3, 4) X(2, 4, 4) X(3, 3, 4) X(3, 4, 4) X(3, 5, 4) X(4, 4, 4) X(4, 5, 4) X(4, 6, 4) \
                     X(5, 5, 2) X(5, 6, 2) X(5, 7, 2) X(6, 6, 2) X(6, 7, 2) X(6, 8, 2) X(7, 7, 1) X(7, 8, 1) X(7, 9, 1) \
                     X(8, 8, 1) X(8, 9, 1) X(8, 10, 1)
@@ -78,8 +78,11 @@ template <int N, int Nq> struct HL {
   static constexpr int VOL = 2 * AB + 3 * BB;
   static constexpr int FIXED = 2 * UA + 12 * N2;
 };
+/* face scratch of one warp: RA = max(T: 4 M^2, QV: 4 Nm^2, BACK1: 3 Nm N), RB = max(S1: 6 Nm M, FLUX: 4 Nm^2) */
+__host__ __device__ static inline int hp_ra_doubles(int NMX, int MX)
+{ int a = 4 * MX * MX, b = 4 * NMX * NMX; return a > b ? a : b; }
 __host__ __device__ static inline int hp_group_doubles(int NMX, int MX)
-{ int rb = 6 * NMX * MX > 4 * NMX * NMX ? 6 * NMX * MX : 4 * NMX * NMX; return 8 * NMX * NMX + rb; }
+{ int rb = 6 * NMX * MX > 4 * NMX * NMX ? 6 * NMX * MX : 4 * NMX * NMX; return hp_ra_doubles(NMX, MX) + rb; }
 
 template <int n> __device__ __forceinline__ void hld(const double *p, int st, double (&x)[n])
 {
@@ -114,60 +117,6 @@ __device__ __forceinline__ void hmat_acc(const double *M, const double (&x)[NI],
     y[o] = s;
   }
 }
-/* dot of a run-time table row (global 1-D pool, uniform address inside a record group) with a register line */
-template <int NI> __device__ __forceinline__ double hdot(const double *__restrict__ row, const double (&x)[NI])
-{
-  double m[NI];
-#pragma unroll
-  for (int i = 0; i < NI; i++) m[i] = __ldg(row + i);
-  double s = 0.;
-#pragma unroll
-  for (int i = 0; i < NI; i++) s = fma(m[i], x[i], s);
-  return s;
-}
-
-/* S1: one face line along axis a (u or du/dn at fixed b) -> mortar points along a:
- *   fld 0: o[q] = E x, o[pl + q] = (E D) x;   fld 1: o[2 pl + q] = E x                                  */
-template <int NP>
-__device__ __forceinline__ void hp_s1_line(const double *in, const double *__restrict__ E, const double *__restrict__ ED,
-                                           int Nm, double *o, int pl, int fld)
-{
-  double x[NP]; hld<NP>(in, 1, x);
-  if (fld == 0) {
-    for (int q = 0; q < Nm; q++) { o[q] = hdot<NP>(E + q * NP, x); o[pl + q] = hdot<NP>(ED + q * NP, x); }
-  } else {
-    for (int q = 0; q < Nm; q++) o[2 * pl + q] = hdot<NP>(E + q * NP, x);
-  }
-}
-/* QV: the three S1 fields at fixed mortar coordinate qa, contracted along b:
- *   out[0] = u, out[(1+ia) Nm2] = du/d(axis a), out[(1+ib) Nm2] = du/d(axis b), out[(1+dn) Nm2] = du/dn      */
-template <int NP>
-__device__ __forceinline__ void hp_qv_line(const double *in, int Nm, int pl, const double *__restrict__ E,
-                                           const double *__restrict__ ED, double *out, int Nm2, int ia, int ib, int dn)
-{
-  double x1[NP], x2[NP], x3[NP];
-  hld<NP>(in, Nm, x1); hld<NP>(in + pl, Nm, x2); hld<NP>(in + 2 * pl, Nm, x3);
-  for (int qb = 0; qb < Nm; qb++) {
-    double e[NP], ed[NP];
-#pragma unroll
-    for (int i = 0; i < NP; i++) { e[i] = __ldg(E + qb * NP + i); ed[i] = __ldg(ED + qb * NP + i); }
-    double su = 0., sa = 0., sb = 0., sn = 0.;
-#pragma unroll
-    for (int i = 0; i < NP; i++) {
-      su = fma(e[i], x1[i], su); sa = fma(e[i], x2[i], sa); sb = fma(ed[i], x1[i], sb); sn = fma(e[i], x3[i], sn);
-    }
-    double *o = out + Nm * qb;
-    o[0] = su; o[(1 + ia) * Nm2] = sa; o[(1 + ib) * Nm2] = sb; o[(1 + dn) * Nm2] = sn;
-  }
-}
-#define HP_NP_SWITCH(np, CALL)                                                                      \
-  switch (np) {                                                                                     \
-    case 2: { constexpr int NP = 2; CALL; } break; case 3: { constexpr int NP = 3; CALL; } break;   \
-    case 4: { constexpr int NP = 4; CALL; } break; case 5: { constexpr int NP = 5; CALL; } break;   \
-    case 6: { constexpr int NP = 6; CALL; } break; case 7: { constexpr int NP = 7; CALL; } break;   \
-    default: { constexpr int NP = 8; CALL; } break;                                                 \
-  }
-
 __device__ __forceinline__ void hp_face_strides(int d, int sj, int sk, int &sa, int &sb, int &sn)
 {
   sa = d == 0 ? sj : 1; sb = d == 2 ? sj : sk; sn = d == 0 ? 1 : (d == 1 ? sj : sk);
@@ -180,13 +129,12 @@ __device__ __forceinline__ int hp_tcode_src(int tcode, int n, int a, int b)
   return x + n * y;
 }
 
-template <int N, int Nq, int NG>
-__global__ void __launch_bounds__(128) d4b_apply_hp_kernel(const hp_args A)
+template <int N, int Nq>
+__global__ void __launch_bounds__(128, (N <= 4 ? 4 : (Nq <= 6 ? 3 : 2))) d4b_apply_hp_kernel(const hp_args A)
 {
   using L = HL<N, Nq>;
   constexpr int N2 = L::N2, N3 = L::N3, Q2 = L::Q2, Q3 = L::Q3, NQ = L::NQ;
   constexpr int SJ = L::SJ, SK = L::SK, AS = L::AS, BS = L::BS;
-  constexpr int GS = 32 / NG;
   extern __shared__ double sm[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slot = blockIdx.x * (blockDim.x >> 5) + warp;
@@ -277,17 +225,17 @@ __global__ void __launch_bounds__(128) d4b_apply_hp_kernel(const hp_args A)
     __syncwarp();
   }
 
-  /* ---------------- faces: NG half-mortar records per round, one per group of GS lanes */
+  /* ---------------- faces: one half-mortar record at a time, all 32 lanes.  Contractions are OUTPUT-stationary:
+   * a lane owns one row of the 1-D table (own side: in registers, N is a template parameter; neighbour side and
+   * the adjoint stages: run-time length, table entries from the L1-resident pool) and sweeps the lines, whose
+   * values come from shared memory as broadcasts. */
   const int MX = A.MX, M2 = MX * MX;
-  const int g = lane / GS, gl = lane % GS;
-  double *RA = S + g * hp_group_doubles(A.NMX, MX), *RB = RA + 8 * A.NMX * A.NMX;
+  double *RA = S, *RB = S + hp_ra_doubles(A.NMX, MX);
   const d4b_ops_dev &ops = c_hp_ops[A.qt];
   const double *pool = ops.pool;
 #pragma unroll 1
-  for (int r0 = 0; r0 < sl.nrec; r0 += NG) {
-    const bool on = r0 + g < sl.nrec;
-    hp_rec R; R.fac_off = 0; R.g_off = -1; R.nbr_u = 0; R.code = 0; R.dims = (N << 8) | Nq;
-    if (on) R = A.recs[sl.rec_begin + r0 + g];
+  for (int r = 0; r < sl.nrec; r++) {
+    const hp_rec R = A.recs[sl.rec_begin + r];
     const int fm = R.code & 7, fp = (R.code >> 3) & 7, tc = (R.code >> 6) & 7;
     const int cm = ((R.code >> 9) & 7) - 1, cp = ((R.code >> 12) & 7) - 1;
     const bool bnd = (R.code >> 15) & 1;
@@ -301,10 +249,12 @@ __global__ void __launch_bounds__(128) d4b_apply_hp_kernel(const hp_args A)
     const double *Pa = pool + ops.idx.I[Np - 1][mdq][cpa], *PaD = pool + ops.idx.ID[Np - 1][mdq][cpa];
     const double *Pb = pool + ops.idx.I[Np - 1][mdq][cpb], *PbD = pool + ops.idx.ID[Np - 1][mdq][cpb];
     const double *F = A.fac + R.fac_off;
-    const int pl = Nm * MX;   /* plane stride of the S1 buffers */
+    const int pl = Nm * MX;                       /* plane stride of the S1 buffers */
+    const int qrow = lane % Nm, qsub = lane / Nm; /* lane = (table row, line subset) for the Nm-row stages */
+    const int SQ = 32 / Nm;                       /* line subsets (lanes >= SQ * Nm idle in those stages)  */
 
-    /* T: traces at face nodes.  RA[0 + t] = u-, RA[M2 + t] = du-/dn, RA[2 M2 + t'] = u+, RA[3 M2 + t'] = du+/dn */
-    if (on) {
+    /* T: traces at face nodes.  RA[t] = u-, RA[M2 + t] = du-/dn, RA[2 M2 + t'] = u+, RA[3 M2 + t'] = du+/dn */
+    {
       int sa, sb, sn; hp_face_strides(d, SJ, SK, sa, sb, sn);
       const int lay = (fm & 1) ? N - 1 : 0;
       const int Np2 = Np * Np, ntask = N2 + (bnd ? 0 : Np2);
@@ -312,7 +262,7 @@ __global__ void __launch_bounds__(128) d4b_apply_hp_kernel(const hp_args A)
       const int pa = dp == 0 ? Np : 1, pb = dp == 2 ? Np : Np2, pn = dp == 0 ? 1 : (dp == 1 ? Np : Np2);
       const int layp = (fp & 1) ? Np - 1 : 0;
       const double *Dp = pool + ops.idx.D[Np - 1] + layp * Np;
-      for (int t = gl; t < ntask; t += GS) {
+      for (int t = lane; t < ntask; t += 32) {
         if (t < N2) {
           const int a = t % N, b = t / N;
           double x[N]; hld<N>(U + a * sa + b * sb, sn, x);
@@ -322,9 +272,10 @@ __global__ void __launch_bounds__(128) d4b_apply_hp_kernel(const hp_args A)
           RA[t] = (fm & 1) ? x[N - 1] : x[0];
           RA[M2 + t] = dn;
         } else {
-          const int tt = t - N2, a = tt % Np, b = tt / Np;
+          const int tt = t - N2, b = tt / Np, a = tt - b * Np;
           const double *p = un + a * pa + b * pb;
           double dn = 0., ul = 0.;
+#pragma unroll 4
           for (int m = 0; m < Np; m++) {
             const double v = __ldg(p + m * pn);
             dn = fma(__ldg(Dp + m), v, dn);
@@ -335,49 +286,91 @@ __global__ void __launch_bounds__(128) d4b_apply_hp_kernel(const hp_args A)
       }
     }
     __syncwarp();
-    /* S1: along face axis a.  RB[(3 side + k) pl + q + Nm b], k = {E u, E D u, E dn} */
-    if (on) {
-      const int ntask = 2 * N + (bnd ? 0 : 2 * Np);
-      for (int t = gl; t < ntask; t += GS) {
-        if (t < 2 * N) {
-          const int fld = t / N, b = t % N;
-          hp_s1_line<N>(RA + fld * M2 + N * b, Ea, EaD, Nm, RB + Nm * b, pl, fld);
-        } else {
-          const int tt = t - 2 * N, fld = tt / Np, b = tt % Np;
-          HP_NP_SWITCH(Np, hp_s1_line<NP>(RA + (2 + fld) * M2 + Np * b, Pa, PaD, Nm, RB + 3 * pl + Nm * b, pl, fld))
+    /* S1: along face axis a.  RB[(3 side + k) pl + q + Nm b], k = {E u, E D u, E dn}; lane = (q, subset of b) */
+    if (qsub < SQ) {
+      {
+        double me[N], md[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) { me[i] = __ldg(Ea + qrow * N + i); md[i] = __ldg(EaD + qrow * N + i); }
+        for (int b = qsub; b < N; b += SQ) {
+          double su = 0., sc = 0., sd = 0.;
+#pragma unroll
+          for (int i = 0; i < N; i++) {
+            const double xu = RA[N * b + i], xn = RA[M2 + N * b + i];
+            su = fma(me[i], xu, su); sc = fma(md[i], xu, sc); sd = fma(me[i], xn, sd);
+          }
+          double *o = RB + qrow + Nm * b;
+          o[0] = su; o[pl] = sc; o[2 * pl] = sd;
+        }
+      }
+      if (!bnd) {
+        const double *pe = Pa + qrow * Np, *pd = PaD + qrow * Np;
+        for (int b = qsub; b < Np; b += SQ) {
+          const double *xu = RA + 2 * M2 + Np * b, *xn = RA + 3 * M2 + Np * b;
+          double su = 0., sc = 0., sd = 0.;
+#pragma unroll 4
+          for (int i = 0; i < Np; i++) {
+            const double e = __ldg(pe + i), ed = __ldg(pd + i), u0 = xu[i], n0 = xn[i];
+            su = fma(e, u0, su); sc = fma(ed, u0, sc); sd = fma(e, n0, sd);
+          }
+          double *o = RB + 3 * pl + qrow + Nm * b;
+          o[0] = su; o[pl] = sc; o[2 * pl] = sd;
         }
       }
     }
     __syncwarp();
-    /* QV: along face axis b.  RA[(4 side + fld) Nm2 + q], fld 0 = u, 1 + l = du/dr_l (l in that side's frame) */
-    if (on) {
-      const int ntask = bnd ? Nm : 2 * Nm;
-      for (int t = gl; t < ntask; t += GS) {
-        if (t < Nm) {
-          hp_qv_line<N>(RB + t, Nm, pl, Eb, EbD, RA + t, Nm2, ia, ib, d);
-        } else {
-          const int qa = t - Nm;
-          HP_NP_SWITCH(Np, hp_qv_line<NP>(RB + 3 * pl + qa, Nm, pl, Pb, PbD, RA + 4 * Nm2 + qa, Nm2, iap, ibp, dp))
+    /* QV: along face axis b, then the fold with the face factors, in MY point order:
+     * RA[q] = u-, RA[Nm2 + q] = sum_l a-_l du-/dr_l, RA[2 Nm2 + q] = u+, RA[3 Nm2 + q] = sum_l a+_l du+/dr_l.
+     * lane = (qb, subset of qa) */
+    if (qsub < SQ) {
+      {
+        double me[N], md[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) { me[i] = __ldg(Eb + qrow * N + i); md[i] = __ldg(EbD + qrow * N + i); }
+        for (int qa = qsub; qa < Nm; qa += SQ) {
+          double su = 0., sa = 0., sb = 0., sn = 0.;
+#pragma unroll
+          for (int i = 0; i < N; i++) {
+            const double x1 = RB[qa + Nm * i], x2 = RB[pl + qa + Nm * i], x3 = RB[2 * pl + qa + Nm * i];
+            su = fma(me[i], x1, su); sa = fma(me[i], x2, sa); sb = fma(md[i], x1, sb); sn = fma(me[i], x3, sn);
+          }
+          const int q = qa + Nm * qrow;
+          RA[q] = su;
+          RA[Nm2 + q] = __ldg(F + ia * Nm2 + q) * sa + __ldg(F + ib * Nm2 + q) * sb + __ldg(F + d * Nm2 + q) * sn;
+        }
+      }
+      if (!bnd) {
+        const double *pe = Pb + qrow * Np, *pd = PbD + qrow * Np;
+        for (int qa = qsub; qa < Nm; qa += SQ) {
+          const double *x1 = RB + 3 * pl + qa, *x2 = x1 + pl, *x3 = x2 + pl;
+          double su = 0., sa = 0., sb = 0., sn = 0.;
+#pragma unroll 4
+          for (int i = 0; i < Np; i++) {
+            const double e = __ldg(pe + i), ed = __ldg(pd + i), v1 = x1[Nm * i], v2 = x2[Nm * i], v3 = x3[Nm * i];
+            su = fma(e, v1, su); sa = fma(e, v2, sa); sb = fma(ed, v1, sb); sn = fma(e, v3, sn);
+          }
+          /* (qa, qrow) is the neighbour's point; mine is */
+          const int xx = (tc & 2) ? Nm - 1 - qa : qa, yy = (tc & 4) ? Nm - 1 - qrow : qrow;
+          const int q = (tc & 1) ? xx + Nm * yy : yy + Nm * xx;
+          RA[2 * Nm2 + q] = su;
+          RA[3 * Nm2 + q] = __ldg(F + (3 + iap) * Nm2 + q) * sa + __ldg(F + (3 + ibp) * Nm2 + q) * sb +
+                            __ldg(F + (3 + dp) * Nm2 + q) * sn;
         }
       }
     }
     __syncwarp();
     /* FLUX at the mortar quadrature points (..._flux_sipg.c:645-677 interior, :139-191 Dirichlet):
      * RB[k Nm2 + q], k = 0: tested with v; 1, 2: tested with dv/d(axis a), dv/d(axis b); 3: with dv/dn */
-    if (on) {
+    {
       const double *wq = pool + ops.idx.w[mdq];
-      for (int q = gl; q < Nm2; q += GS) {
-        const int a = q % Nm, b = q / Nm;
+      for (int q = lane; q < Nm2; q += 32) {
+        const int b = q / Nm, a = q - b * Nm;
         const double w = __ldg(wq + a) * __ldg(wq + b);
         const double am0 = __ldg(F + q), am1 = __ldg(F + Nm2 + q), am2 = __ldg(F + 2 * Nm2 + q);
-        const double um = RA[q];
-        const double qm = am0 * RA[Nm2 + q] + am1 * RA[2 * Nm2 + q] + am2 * RA[3 * Nm2 + q];
+        const double um = RA[q], qm = RA[Nm2 + q];
         double jump, t1, sjs, hs;
         if (!bnd) {
-          const int s = hp_tcode_src(tc, Nm, a, b);
-          const double qp = __ldg(F + 3 * Nm2 + q) * RA[5 * Nm2 + s] + __ldg(F + 4 * Nm2 + q) * RA[6 * Nm2 + s] +
-                            __ldg(F + 5 * Nm2 + q) * RA[7 * Nm2 + s];
-          jump = um - RA[4 * Nm2 + s]; t1 = -0.5 * (qm + qp); sjs = __ldg(F + 6 * Nm2 + q); hs = -0.5;
+          jump = um - RA[2 * Nm2 + q]; t1 = -0.5 * (qm + RA[3 * Nm2 + q]); sjs = __ldg(F + 6 * Nm2 + q); hs = -0.5;
         } else {
           const double gv = R.g_off >= 0 ? __ldg(A.bc_g + R.g_off + q) : 0.;
           jump = um - gv; t1 = -qm; sjs = __ldg(F + 3 * Nm2 + q); hs = -1.0;
@@ -390,59 +383,44 @@ __global__ void __launch_bounds__(128) d4b_apply_hp_kernel(const hp_args A)
       }
     }
     __syncwarp();
-    /* BACK1: adjoint of QV along b.  RA[k NmN + qa + Nm j], k = 0: Eb^T F + (Eb D)^T Hb, 1: Eb^T Ha, 2: Eb^T Hn */
+    /* BACK1: adjoint of QV along b.  RA[k NmN + qa + Nm j], k = 0: Eb^T F + (Eb D)^T Hb, 1: Eb^T Ha, 2: Eb^T Hn;
+     * lane = (j, subset of qa) */
     const int NmN = Nm * N;
-    if (on) {
-      for (int t = gl; t < 3 * Nm; t += GS) {
-        const int k = t / Nm, qa = t % Nm;
-        double y[N];
-#pragma unroll
-        for (int j = 0; j < N; j++) y[j] = 0.;
-        const double *f0 = RB + (k == 0 ? 0 : (k == 1 ? Nm2 : 3 * Nm2)) + qa;
+    constexpr int SN = 32 / N;
+    const int jrow = lane % N, jsub = lane / N;
+    if (jsub < SN) {
+      for (int qa = jsub; qa < Nm; qa += SN) {
+        double x1 = 0., ha = 0., hn = 0.;
+        const double *f0 = RB + qa;
+#pragma unroll 4
         for (int qb = 0; qb < Nm; qb++) {
-          const double v = f0[Nm * qb];
-#pragma unroll
-          for (int j = 0; j < N; j++) y[j] = fma(__ldg(Eb + qb * N + j), v, y[j]);
-          if (k == 0) {
-            const double v2 = RB[2 * Nm2 + qa + Nm * qb];
-#pragma unroll
-            for (int j = 0; j < N; j++) y[j] = fma(__ldg(EbD + qb * N + j), v2, y[j]);
-          }
+          const double e = __ldg(Eb + qb * N + jrow), ed = __ldg(EbD + qb * N + jrow);
+          const double v0 = f0[Nm * qb], v1 = f0[Nm2 + Nm * qb], v2 = f0[2 * Nm2 + Nm * qb], v3 = f0[3 * Nm2 + Nm * qb];
+          x1 = fma(e, v0, x1); x1 = fma(ed, v2, x1); ha = fma(e, v1, ha); hn = fma(e, v3, hn);
         }
-        hst<N>(RA + k * NmN + qa, Nm, y);
+        double *o = RA + qa + Nm * jrow;
+        o[0] = x1; o[NmN] = ha; o[2 * NmN] = hn;
       }
     }
     __syncwarp();
-    /* BACK2: adjoint of S1 along a.  RB[k N2 + a' + N b'], k = 0: Y (lifted onto the face layer), 1: Z (normal lift) */
-    if (on) {
-      for (int t = gl; t < 2 * N; t += GS) {
-        const int k = t / N, bp = t % N;
-        double y[N];
-#pragma unroll
-        for (int j = 0; j < N; j++) y[j] = 0.;
-        const double *x1 = RA + (k == 0 ? 0 : 2 * NmN) + Nm * bp;
+    /* BACK2: adjoint of S1 along a, accumulated straight into the per-face Y (lift onto the face layer) and
+     * Z (normal-derivative lift); lane = (a', subset of b') */
+    if (jsub < SN) {
+      double *yz = YZ + fm * 2 * N2;
+      for (int bp = jsub; bp < N; bp += SN) {
+        double y = 0., z = 0.;
+        const double *x1 = RA + Nm * bp;
+#pragma unroll 4
         for (int qa = 0; qa < Nm; qa++) {
-          const double v = x1[qa];
-#pragma unroll
-          for (int j = 0; j < N; j++) y[j] = fma(__ldg(Ea + qa * N + j), v, y[j]);
-          if (k == 0) {
-            const double v2 = RA[NmN + Nm * bp + qa];
-#pragma unroll
-            for (int j = 0; j < N; j++) y[j] = fma(__ldg(EaD + qa * N + j), v2, y[j]);
-          }
+          const double e = __ldg(Ea + qa * N + jrow), ed = __ldg(EaD + qa * N + jrow);
+          y = fma(e, x1[qa], y); y = fma(ed, x1[NmN + qa], y); z = fma(e, x1[2 * NmN + qa], z);
         }
-        hst<N>(RB + k * N2 + N * bp, 1, y);
+        yz[jrow + N * bp] += y; yz[N2 + jrow + N * bp] += z;
       }
     }
     __syncwarp();
-    /* accumulate per face, groups in fixed order (children of one face share Y, Z) */
-#pragma unroll
-    for (int gg = 0; gg < NG; gg++) {
-      if (g == gg && on)
-        for (int t = gl; t < 2 * N2; t += GS) YZ[fm * 2 * N2 + t] += RB[t];
-      __syncwarp();
-    }
   }
+
 
   /* ---------------- LIFT (..._flux_sipg.c:918-958): face layer += Y, normal line += D[layer,:] Z; then store */
 #pragma unroll 1
@@ -477,16 +455,16 @@ bool d4b_hp_supported(int N, int Nq)
   return false;
 }
 
-template <int N, int Nq> static size_t hp_warp_doubles(int NMX, int MX, int NG)
+template <int N, int Nq> static size_t hp_warp_doubles(int NMX, int MX)
 {
   using L = HL<N, Nq>;
-  int scr = NG * hp_group_doubles(NMX, MX);
+  int scr = hp_group_doubles(NMX, MX);
   if (scr < L::VOL) scr = L::VOL;
   return (size_t)L::FIXED + scr;
 }
 static size_t hp_warp_doubles_rt(int N, int Nq, int NMX, int MX)
 {
-#define X(a, b, g) if (N == a && Nq == b) return hp_warp_doubles<a, b>(NMX, MX, g);
+#define X(a, b, g) if (N == a && Nq == b) return hp_warp_doubles<a, b>(NMX, MX);
   HP_PAIRS(X)
 #undef X
   return (size_t)1 << 40;
@@ -561,7 +539,7 @@ static int hp_bind_ops(int qt)
   return D4B_OK;
 }
 
-template <int N, int Nq, int NG>
+template <int N, int Nq>
 static int hp_launch_bucket(const d4b_mesh *m, const d4b_hp_bucket &b, const double *u, double *Au, cudaStream_t st)
 {
   /* the element's own tables live in a __constant__ block of this instance: written once; a level with the
@@ -584,19 +562,19 @@ static int hp_launch_bucket(const d4b_mesh *m, const d4b_hp_bucket &b, const dou
     D4B_CUDA((hp_const<N, Nq>::put(&t)));
     have_qt = m->quad_type;
   }
-  const size_t per_warp = hp_warp_doubles<N, Nq>(b.NMX, b.MX, NG);
+  const size_t per_warp = hp_warp_doubles<N, Nq>(b.NMX, b.MX);
   int wpb = 4;
-  while (wpb > 1 && wpb * per_warp * 8 > 110 * 1024) wpb >>= 1;   /* two CTAs per SM where it fits */
+  while (wpb > 1 && wpb * per_warp * 8 > 110 * 1024) wpb >>= 1;   /* at least two CTAs per SM */
   const size_t smem = wpb * per_warp * 8;
   if (smem > attr_smem) {
-    D4B_CUDA(cudaFuncSetAttribute(d4b_apply_hp_kernel<N, Nq, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(d4b_apply_hp_kernel<N, Nq>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_smem = smem;
   }
   hp_args A;
   A.slots = (const hp_slot *)b.slots; A.recs = (const hp_rec *)b.recs; A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
   A.u = u; A.u_ghost = m->u_ghost; A.Au = Au; A.n_list = b.count; A.qt = m->quad_type; A.NMX = b.NMX; A.MX = b.MX;
   A.per_warp = (int)per_warp;
-  d4b_apply_hp_kernel<N, Nq, NG><<<(b.count + wpb - 1) / wpb, 32 * wpb, smem, st>>>(A);
+  d4b_apply_hp_kernel<N, Nq><<<(b.count + wpb - 1) / wpb, 32 * wpb, smem, st>>>(A);
   D4B_CUDA(cudaGetLastError());
   d4b_count_launch(1);
   return D4B_OK;
@@ -610,7 +588,7 @@ int d4b_launch_hp(const d4b_mesh *m, const double *u, double *Au, cudaStream_t s
   for (int i = 0; i < m->n_hp; i++) {
     const d4b_hp_bucket &b = m->hp[i];
     rc = D4B_EINVAL;
-#define X(a, c, g) if (b.N == a && b.Nq == c) rc = hp_launch_bucket<a, c, g>(m, b, u, Au, st);
+#define X(a, c, g) if (b.N == a && b.Nq == c) rc = hp_launch_bucket<a, c>(m, b, u, Au, st);
     HP_PAIRS(X)
 #undef X
     if (rc != D4B_OK) return rc;
