@@ -98,6 +98,16 @@ const d4b_ops_dev *d4b_ops_device(int qt)
   return &g_ops[qt];
 }
 
+int d4b_mesh_make_streams(d4b_mesh *m)
+{
+  for (int k = 0; k < D4B_NSIDE; k++) {
+    D4B_CUDA(cudaStreamCreateWithFlags(&m->side[k], cudaStreamNonBlocking));
+    D4B_CUDA(cudaEventCreateWithFlags(&m->ev_join[k], cudaEventDisableTiming));
+  }
+  D4B_CUDA(cudaEventCreateWithFlags(&m->ev_fork, cudaEventDisableTiming));
+  return D4B_OK;
+}
+
 template <class T> static int upload(T **dst, const T *src, size_t n, int64_t *bytes)
 {
   *dst = nullptr;
@@ -186,6 +196,7 @@ int d4b_mesh_create(const d4b_mesh_desc_t *D, d4b_mesh_t **out)
     D4B_CUDA(cudaMalloc((void **)&m->send_buf, (sn ? sn : 1) * sizeof(double)));
   }
   if ((rc = d4b_fast_classify(m, D)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
+  if ((rc = d4b_mesh_make_streams(m)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
   *out = m;
   return D4B_OK;
 }
@@ -201,6 +212,8 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   cudaFree(m->generic_list);
   free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
   free(m->send_node_begin_h); free(m->recv_node_begin_h);
+  for (int k = 0; k < D4B_NSIDE; k++) { if (m->side[k]) cudaStreamDestroy(m->side[k]); if (m->ev_join[k]) cudaEventDestroy(m->ev_join[k]); }
+  if (m->ev_fork) cudaEventDestroy(m->ev_fork);
   if (m->stream) cudaStreamDestroy(m->stream);
   if (m->copy_stream) { cudaStreamDestroy(m->copy_stream); cudaStreamDestroy(m->in_stream); for (int k = 0; k < D4B_PIPE_MAX; k++) { cudaEventDestroy(m->ev_out[k]); cudaEventDestroy(m->ev_in[k]); } cudaEventDestroy(m->ev_done);
     cudaFree(m->pipe_late.elem_list); cudaFree(m->pipe_late.frec); cudaFree(m->pipe_late.nrec); cudaFree(m->pipe_late.v3_slots); }

@@ -19,7 +19,21 @@
 #define FAST_MAXN 8
 #define FAST_MAXQ 10
 struct fast_tab { double B[FAST_MAXQ * FAST_MAXN], C[FAST_MAXQ * FAST_MAXN], D[FAST_MAXN * FAST_MAXN], w[FAST_MAXQ]; };
-__constant__ fast_tab c_ft;
+#define FAST_PAIRS(X) X(2,2) X(2,3) X(2,4) X(3,3) X(3,4) X(3,5) X(4,4) X(4,5) X(4,6) X(5,5) X(5,6) X(5,7) \
+                      X(6,6) X(6,7) X(6,8) X(7,7) X(7,8) X(8,8) X(8,9)
+/* one immutable table per template instance (written once per quadrature type): launches of different
+ * instances on different streams never race on it */
+enum {
+#define X(a, b) FTI_##a##_##b,
+  FAST_PAIRS(X)
+#undef X
+  FAST_NINST
+};
+template <int N, int Nq> struct fast_index;
+#define X(a, b) template <> struct fast_index<a, b> { static constexpr int value = FTI_##a##_##b; };
+FAST_PAIRS(X)
+#undef X
+__constant__ fast_tab c_fts[FAST_NINST];
 
 struct fast_args {
   const int64_t *node_off; const int64_t *quad_off; const double *G; const int32_t *hm_begin;
@@ -104,6 +118,7 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
   const v3_slot *sl = A.slots + (active ? slot : 0);
   double *U = sm + le * L::PER, *ACC = U + L::UA, *S = ACC + L::UA;
   double *V0 = S, *V1 = S + L::AB, *V2 = S + 2 * L::AB, *V3 = V2 + L::BB, *V4 = V3 + L::BB;
+  const fast_tab &c_ft = c_fts[fast_index<N, Nq>::value];
   const double *B = c_ft.B, *C = c_ft.C, *D = c_ft.D;
   const double *ue = A.u + __ldg(&sl->node_off);
   const int fa = lt % N, fb = lt / N; /* my face node (T stage) */
@@ -407,9 +422,6 @@ static int launch_bucket(const d4b_mesh *m, const d4b_fast_bucket &b, const doub
   return D4B_OK;
 }
 
-#define FAST_PAIRS(X) X(2,2) X(2,3) X(2,4) X(3,3) X(3,4) X(3,5) X(4,4) X(4,5) X(4,6) X(5,5) X(5,6) X(5,7) \
-                      X(6,6) X(6,7) X(6,8) X(7,7) X(7,8) X(8,8) X(8,9)
-
 bool d4b_fast_supported(int N, int Nq)
 {
 #define X(a, b) if (N == a && Nq == b) return true;
@@ -420,21 +432,17 @@ bool d4b_fast_supported(int N, int Nq)
 
 static int upload_tab(int qt, int N, int Nq, cudaStream_t st)
 {
-  /* one pinned, immutable host copy per (quadrature, N, Nq): an enqueued asynchronous copy to constant
-   * memory may execute long after this call returns, so its source must never be rewritten */
-  static int cur_key = -1;
-  static cudaStream_t cur_st = nullptr;   /* a table enqueued on another stream is not ordered before this launch */
-  static fast_tab *cache[2 * 16 * 16] = {nullptr};
-  const int key = (qt * 16 + N) * 16 + Nq;
-  if (cur_key == key && cur_st == st) return D4B_OK;
-  cur_st = st;
-  if (cache[key]) {
-    D4B_CUDA(cudaMemcpyToSymbolAsync(c_ft, cache[key], sizeof(fast_tab), 0, cudaMemcpyHostToDevice, st));
-    cur_key = key;
-    return D4B_OK;
-  }
-  fast_tab *t = nullptr;
-  D4B_CUDA(cudaMallocHost((void **)&t, sizeof(fast_tab)));
+  static int have_qt[FAST_NINST];
+  static bool init = false;
+  if (!init) { for (int i = 0; i < FAST_NINST; i++) have_qt[i] = -1; init = true; }
+  int idx = -1;
+#define X(a, c) if (N == a && Nq == c) idx = FTI_##a##_##c;
+  FAST_PAIRS(X)
+#undef X
+  if (idx < 0) { d4b_set_error("no line-task instance for N=%d Nq=%d", N, Nq); return D4B_EINVAL; }
+  if (have_qt[idx] == qt) return D4B_OK;
+  if (have_qt[idx] != -1) D4B_CUDA(cudaDeviceSynchronize());   /* other quadrature type still in flight */
+  fast_tab tt, *t = &tt;
   memset(t, 0, sizeof *t);
   double I[D4B_OPS_MAXN * D4B_OPS_MAXN], Dm[D4B_OPS_MAXN * D4B_OPS_MAXN], x[D4B_OPS_MAXN], w[D4B_OPS_MAXN];
   d4b_ops_interp(N - 1, Nq - 1, qt, -1, I); d4b_ops_diff(N - 1, Dm); d4b_ops_quad(Nq - 1, qt, x, w);
@@ -448,31 +456,60 @@ static int upload_tab(int qt, int N, int Nq, cudaStream_t st)
     }
   }
   for (int i = 0; i < N * N; i++) t->D[i] = Dm[i];
-  cache[key] = t;
-  D4B_CUDA(cudaMemcpyToSymbolAsync(c_ft, t, sizeof(fast_tab), 0, cudaMemcpyHostToDevice, st));
-  cur_key = key;
+  D4B_CUDA(cudaMemcpyToSymbol(c_fts, t, sizeof(fast_tab), (size_t)idx * sizeof(fast_tab), cudaMemcpyHostToDevice));
+  D4B_CUDA(cudaDeviceSynchronize());   /* the staged copy has landed before any stream launches */
+  (void)st;
+  have_qt[idx] = qt;
   return D4B_OK;
 }
 
+static int launch_fast_bucket(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st)
+{
+  if (b.nrec && d4b_v3_supported(b.N, b.Nq)) return d4b_launch_v3(m, b, u, Au, st);
+  int rc = upload_tab(m->quad_type, b.N, b.Nq, st);
+  if (rc != D4B_OK) return rc;
+  rc = D4B_EINVAL;
+#define X(a, c) if (b.N == a && b.Nq == c) rc = launch_bucket<a, c>(m, b, u, Au, st);
+  FAST_PAIRS(X)
+#undef X
+  return rc;
+}
+
+/* One apply = one launch per degree bucket (regular-element kernels, hp kernel) + the completeness kernel.
+ * Buckets write disjoint elements of Au and only read u, so with more than one launch they run CONCURRENTLY:
+ * fork from the caller's stream to the level's side streams, largest bucket first, join back.  A random-hp
+ * level has 8-12 launches of very different size; run back to back the small ones cost a launch latency each
+ * and the tail of every large one leaves SMs idle. */
 int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st, int *handled)
 {
   *handled = 1;
-  for (int i = 0; i < m->n_fast; i++) {
-    const d4b_fast_bucket &b = m->fast[i];
-    if (b.nrec && d4b_v3_supported(b.N, b.Nq)) {
-      int rc3 = d4b_launch_v3(m, b, u, Au, st);
-      if (rc3 != D4B_OK) return rc3;
-      continue;
+  struct item { int kind, idx; double w; };
+  item it[2 * D4B_MAX_BUCKETS + 1];
+  int n = 0;
+  for (int i = 0; i < m->n_fast; i++) it[n++] = {0, i, (double)m->fast[i].count * m->fast[i].Nq * m->fast[i].Nq * m->fast[i].Nq};
+  for (int i = 0; i < m->n_hp; i++) it[n++] = {1, i, 4.0 * m->hp[i].n_rec / 6.0 * m->hp[i].Nq * m->hp[i].Nq * m->hp[i].Nq};
+  if (m->n_generic > 0) it[n++] = {2, 0, 40.0 * m->n_generic * 64};
+  for (int i = 1; i < n; i++) { item x = it[i]; int j = i; while (j > 0 && it[j - 1].w < x.w) { it[j] = it[j - 1]; j--; } it[j] = x; }
+  static const bool serial = getenv("D4B_NO_CONCURRENT") != nullptr;
+  const bool fork = n > 1 && !serial && m->ev_fork;
+  int used = 0;
+  if (fork) D4B_CUDA(cudaEventRecord(m->ev_fork, st));
+  for (int i = 0; i < n; i++) {
+    cudaStream_t s = st;
+    if (fork && i > 0) {
+      const int k = (i - 1) % D4B_NSIDE;
+      s = m->side[k];
+      if (k >= used) { D4B_CUDA(cudaStreamWaitEvent(s, m->ev_fork, 0)); used = k + 1; }
     }
-    int rc = upload_tab(m->quad_type, b.N, b.Nq, st);
-    if (rc != D4B_OK) return rc;
-    rc = D4B_EINVAL;
-#define X(a, c) if (b.N == a && b.Nq == c) rc = launch_bucket<a, c>(m, b, u, Au, st);
-    FAST_PAIRS(X)
-#undef X
+    int rc;
+    if (it[i].kind == 0) rc = launch_fast_bucket(m, m->fast[it[i].idx], u, Au, s);
+    else if (it[i].kind == 1) rc = d4b_launch_hp_bucket(m, it[i].idx, u, Au, s);
+    else rc = d4b_launch_generic(m, u, Au, m->generic_list, m->n_generic, s);
     if (rc != D4B_OK) return rc;
   }
-  { int rch = d4b_launch_hp(m, u, Au, st); if (rch != D4B_OK) return rch; }
-  if (m->n_generic > 0) return d4b_launch_generic(m, u, Au, m->generic_list, m->n_generic, st);
+  for (int k = 0; k < used; k++) {
+    D4B_CUDA(cudaEventRecord(m->ev_join[k], m->side[k]));
+    D4B_CUDA(cudaStreamWaitEvent(st, m->ev_join[k], 0));
+  }
   return D4B_OK;
 }

@@ -253,6 +253,7 @@ int d4b_launch_generic(const d4b_mesh *m, const double *u, double *Au, const int
     if (!ops) return D4B_ECUDA;
     D4B_CUDA(cudaMemcpyToSymbol(c_ops, ops, sizeof(d4b_ops_dev), m->quad_type * sizeof(d4b_ops_dev),
                                 cudaMemcpyHostToDevice));
+    D4B_CUDA(cudaDeviceSynchronize());
     bound[m->quad_type] = true;
   }
   d4b_gen_args A;

@@ -535,6 +535,7 @@ static int hp_bind_ops(int qt)
   const d4b_ops_dev *ops = d4b_ops_device(qt);
   if (!ops) return D4B_ECUDA;
   D4B_CUDA(cudaMemcpyToSymbol(c_hp_ops, ops, sizeof(d4b_ops_dev), qt * sizeof(d4b_ops_dev), cudaMemcpyHostToDevice));
+  D4B_CUDA(cudaDeviceSynchronize());
   bound[qt] = true;
   return D4B_OK;
 }
@@ -560,6 +561,7 @@ static int hp_launch_bucket(const d4b_mesh *m, const d4b_hp_bucket &b, const dou
       }
     for (int i = 0; i < N * N; i++) t.D[i] = Dm[i];
     D4B_CUDA((hp_const<N, Nq>::put(&t)));
+    D4B_CUDA(cudaDeviceSynchronize());   /* the staged copy has landed before any stream launches */
     have_qt = m->quad_type;
   }
   const size_t per_warp = hp_warp_doubles<N, Nq>(b.NMX, b.MX);
@@ -580,18 +582,14 @@ static int hp_launch_bucket(const d4b_mesh *m, const d4b_hp_bucket &b, const dou
   return D4B_OK;
 }
 
-int d4b_launch_hp(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st)
+int d4b_launch_hp_bucket(const d4b_mesh *m, int i, const double *u, double *Au, cudaStream_t st)
 {
-  if (m->n_hp == 0) return D4B_OK;
   int rc = hp_bind_ops(m->quad_type);
   if (rc != D4B_OK) return rc;
-  for (int i = 0; i < m->n_hp; i++) {
-    const d4b_hp_bucket &b = m->hp[i];
-    rc = D4B_EINVAL;
+  const d4b_hp_bucket &b = m->hp[i];
+  rc = D4B_EINVAL;
 #define X(a, c, g) if (b.N == a && b.Nq == c) rc = hp_launch_bucket<a, c>(m, b, u, Au, st);
-    HP_PAIRS(X)
+  HP_PAIRS(X)
 #undef X
-    if (rc != D4B_OK) return rc;
-  }
-  return D4B_OK;
+  return rc;
 }

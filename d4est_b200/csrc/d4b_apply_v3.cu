@@ -38,7 +38,20 @@ struct v3_tab {
   double ed[2][V3_MAXQ];         /* its derivative at -1 / +1  (= Dq^T e)              */
   double w[V3_MAXQ];
 };
-__constant__ v3_tab c_v3;
+/* one immutable table per template instance: written once (per quadrature type), so launches of different
+ * instances on different streams never race on it */
+#define V3_PAIRS(X) X(2, 2) X(2, 4) X(4, 4)
+enum {
+#define X(a, b) V3I_##a##_##b,
+  V3_PAIRS(X)
+#undef X
+  V3_NINST
+};
+template <int N, int Nq> struct v3_index;
+#define X(a, b) template <> struct v3_index<a, b> { static constexpr int value = V3I_##a##_##b; };
+V3_PAIRS(X)
+#undef X
+__constant__ v3_tab c_v3s[V3_NINST];
 
 #define FULL 0xffffffffu
 
@@ -212,8 +225,6 @@ __device__ __forceinline__ double ldg_pin(const double *p)
   return v;
 }
 
-#define V3_PAIRS(X) X(2, 2) X(2, 4) X(4, 4)
-
 template <int N, int Nq> struct V3 {
   static constexpr int TPE = Nq, EPW = 32 / Nq, Q2 = Nq * Nq, Q3 = Q2 * Nq, N2 = N * N, N3 = N2 * N;
   static constexpr bool SWZ = (N == 4 && Nq == 4);   /* XOR-swizzled 64-double element blocks      */
@@ -272,6 +283,7 @@ template <int N, int Nq>
 __device__ __forceinline__ void v3_nbr_trace(double *S, int f_p)
 {
   constexpr int N2 = N * N, Q2 = Nq * Nq;
+  const v3_tab &c_v3 = c_v3s[v3_index<N, Nq>::value];
   const int dp = f_p >> 1;
   const int sa = dp == 0 ? N : 1, sb = dp == 2 ? N : N2, sn = dp == 0 ? 1 : (dp == 1 ? N : N2);
   const int lay = (f_p & 1) ? (N - 1) * sn : 0;
@@ -326,7 +338,7 @@ __device__ __forceinline__ bool v3_is_ext(int code) { return !v3_is_bnd(code) &&
  * at the same points (ignored on the boundary).
  * out: F (tested with v), Hr/Hs/Ht (tested with dv/dr_l). */
 template <int Nq, bool FIRST_FIXED>
-__device__ __forceinline__ void v3_flux(const v3_args &A, int code, const v3_face *fc, int t,
+__device__ __forceinline__ void v3_flux(const v3_tab &c_v3, const v3_args &A, int code, const v3_face *fc, int t,
                                         const double (&a)[4][Nq], const double (&ut)[Nq], const double (&qm)[Nq],
                                         const double (&up)[Nq], const double (&qp)[Nq], double (&F)[Nq],
                                         double (&Hr)[Nq], double (&Hs)[Nq], double (&Ht)[Nq])
@@ -428,6 +440,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
   double *NS = W, *BX = NS + L::NSS, *BY = BX + L::BUF, *BZ = BY + L::BUF, *HT = BZ + L::BUF;
   uint64_t *bar = reinterpret_cast<uint64_t *>(NS + L::SD);
   const int le = lane / TPE, t = lane % TPE;
+  const v3_tab &c_v3 = c_v3s[v3_index<N, Nq>::value];
   const double *B = c_v3.B, *Dq = c_v3.Dq;
 #define TI(a, b, c) L::ti(a, b, c, le)
   if (lane == 0) { mbar_init(bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
@@ -603,7 +616,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
 #pragma unroll
         for (int s = 0; s < 2; s++) {
           double F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
-          v3_flux<Nq, false>(A, fcode[s], &sl->f[s], t, fa[s], ut2[s], qm2[s], up[s], qp[s], F, Hr, Hs, Ht);
+          v3_flux<Nq, false>(c_v3, A, fcode[s], &sl->f[s], t, fa[s], ut2[s], qm2[s], up[s], qp[s], F, Hr, Hs, Ht);
 #pragma unroll
           for (int b = 0; b < Nq; b++) {
             double s0 = F[b];
@@ -678,7 +691,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
 #pragma unroll
       for (int s = 0; s < 2; s++) {
         double F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
-        v3_flux<Nq, true>(A, fcode[s], &sl->f[2 + s], t, fa[s], ut2[s], qm2[s], up[s], qp[s], F, Hr, Hs, Ht);
+        v3_flux<Nq, true>(c_v3, A, fcode[s], &sl->f[2 + s], t, fa[s], ut2[s], qm2[s], up[s], qp[s], F, Hr, Hs, Ht);
 #pragma unroll
         for (int c = 0; c < Nq; c++) {
           double s0 = F[c];
@@ -757,7 +770,7 @@ __global__ void __launch_bounds__(V3<N, Nq>::THREADS, V3<N, Nq>::CTAS) d4b_apply
 #pragma unroll
       for (int s = 0; s < 2; s++) {
         double F[Nq], Hr[Nq], Hs[Nq], Ht[Nq];
-        v3_flux<Nq, true>(A, fcode[s], &sl->f[4 + s], t, fa[s], ut2[s], qm2[s], up[s], qp[s], F, Hr, Hs, Ht);
+        v3_flux<Nq, true>(c_v3, A, fcode[s], &sl->f[4 + s], t, fa[s], ut2[s], qm2[s], up[s], qp[s], F, Hr, Hs, Ht);
 #pragma unroll
         for (int b = 0; b < Nq; b++) {
           double s0 = F[b];
@@ -896,21 +909,19 @@ bool d4b_v3_supported(int N, int Nq)
 
 static int v3_upload_tab(int qt, int N, int Nq, cudaStream_t st)
 {
-  /* one pinned, immutable host copy per (quadrature, N, Nq): the asynchronous copy to constant memory may
-   * execute long after this call returns, so the source of an enqueued copy must never be rewritten */
-  static int cur_key = -1;
-  static cudaStream_t cur_st = nullptr;   /* a table enqueued on another stream is not ordered before this launch */
-  static v3_tab *cache[2 * 16 * 16] = {nullptr};
-  const int key = (qt * 16 + N) * 16 + Nq;
-  if (cur_key == key && cur_st == st) return D4B_OK;
-  cur_st = st;
-  if (cache[key]) {
-    D4B_CUDA(cudaMemcpyToSymbolAsync(c_v3, cache[key], sizeof(v3_tab), 0, cudaMemcpyHostToDevice, st));
-    cur_key = key;
-    return D4B_OK;
-  }
-  v3_tab *t = nullptr;
-  D4B_CUDA(cudaMallocHost((void **)&t, sizeof(v3_tab)));
+  /* each instance has its own __constant__ slot, written once; a level with the other quadrature type waits
+   * for everything in flight on the device before the slot is rewritten */
+  static int have_qt[V3_NINST];
+  static bool init = false;
+  if (!init) { for (int i = 0; i < V3_NINST; i++) have_qt[i] = -1; init = true; }
+  int idx = -1;
+#define X(a, c) if (N == a && Nq == c) idx = V3I_##a##_##c;
+  V3_PAIRS(X)
+#undef X
+  if (idx < 0) { d4b_set_error("no register-blocked instance for N=%d Nq=%d", N, Nq); return D4B_EINVAL; }
+  if (have_qt[idx] == qt) return D4B_OK;
+  if (have_qt[idx] != -1) D4B_CUDA(cudaDeviceSynchronize());
+  v3_tab tt, *t = &tt;
   memset(t, 0, sizeof *t);
   double I[D4B_OPS_MAXN * D4B_OPS_MAXN], Dm[D4B_OPS_MAXN * D4B_OPS_MAXN], Dqm[D4B_OPS_MAXN * D4B_OPS_MAXN];
   double x[D4B_OPS_MAXN], w[D4B_OPS_MAXN], e0[D4B_OPS_MAXN], e1[D4B_OPS_MAXN];
@@ -925,9 +936,10 @@ static int v3_upload_tab(int qt, int N, int Nq, cudaStream_t st)
     for (int a = 0; a < Nq; a++) { s0 += e0[a] * Dqm[a * Nq + m]; s1 += e1[a] * Dqm[a * Nq + m]; }
     t->ed[0][m] = s0; t->ed[1][m] = s1;
   }
-  cache[key] = t;
-  D4B_CUDA(cudaMemcpyToSymbolAsync(c_v3, t, sizeof(v3_tab), 0, cudaMemcpyHostToDevice, st));
-  cur_key = key;
+  D4B_CUDA(cudaMemcpyToSymbol(c_v3s, t, sizeof(v3_tab), (size_t)idx * sizeof(v3_tab), cudaMemcpyHostToDevice));
+  D4B_CUDA(cudaDeviceSynchronize());   /* the staged copy has landed before any stream launches */
+  (void)st;
+  have_qt[idx] = qt;
   return D4B_OK;
 }
 

@@ -57,6 +57,8 @@ struct d4b_mesh {
   d4b_fast_bucket pipe_late;       /* elements with a face neighbour more than one chunk ahead: computed after the last upload */
   d4b_fast_bucket fast[D4B_MAX_BUCKETS]; int n_fast;
   d4b_hp_bucket hp[D4B_MAX_BUCKETS]; int n_hp;
+  #define D4B_NSIDE 6
+  cudaStream_t side[D4B_NSIDE]; cudaEvent_t ev_fork, ev_join[D4B_NSIDE];   /* concurrent bucket launches of one apply */
   int32_t *generic_list; int n_generic;   /* elements left to the generic kernel */
 };
 
@@ -83,7 +85,7 @@ const d4b_ops_dev *d4b_ops_device(int quad_type); /* lazily built + uploaded */
 void d4b_count_launch(int n);
 bool d4b_fast_supported(int N, int Nq);
 bool d4b_hp_supported(int N, int Nq);
-int d4b_launch_hp(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st);
+int d4b_launch_hp_bucket(const d4b_mesh *m, int i, const double *u, double *Au, cudaStream_t st);
 bool d4b_v3_supported(int N, int Nq);
 int d4b_launch_v3(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st);
 int d4b_launch_v3_range(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st,
@@ -93,6 +95,7 @@ int d4b_v3_build_late(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges,
 int d4b_v3_range_need(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, const int *bounds, int *need_host, cudaStream_t st);
 /* split elements into fast buckets + generic list; D->hm == NULL means the uniform device-built brick */
 int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D);
+int d4b_mesh_make_streams(d4b_mesh *m);
 
 #define D4B_CUDA(call)                                                                   \
   do { cudaError_t e_ = (call);                                                          \
