@@ -83,6 +83,7 @@ SYMBOLS = {
     "d4b_cg_eigs": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.POINTER(C.c_double), _P, _P]),
     "d4b_cg_solve": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_double), _P, _P]),
     "d4b_fcg_solve": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, _P, _P, C.POINTER(C.c_int), C.POINTER(C.c_double), _P, _P]),
+    "d4b_set_option": (C.c_int, [C.c_char_p, C.c_int]),
     "d4b_mg_transfer_create": (C.c_int, [C.c_int, _P, _P, _P, _P, _P, C.POINTER(_P)]),
     "d4b_mg_transfer_destroy": (None, [_P]),
     "d4b_mg_restrict": (C.c_int, [_P, _P, _P, _P]),
@@ -93,6 +94,12 @@ SYMBOLS = {
     "d4b_mg_vcycle": (C.c_int, [_P, _P, _P, C.POINTER(C.c_double), _P]),
     "d4b_mg_solve": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int), C.POINTER(C.c_double), _P]),
     "d4b_mg_pc_apply": (C.c_int, [_P, _P, _P, _P]),
+    "d4b_mg_num_levels": (C.c_int, [_P]),
+    "d4b_residual_dev": (C.c_int, [_P, _P, _P, _P, _P]),
+    "d4b_residual_host": (C.c_int, [_P, _P, _P, _P]),
+    "d4b_cheby_smooth_host": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.POINTER(C.c_double)]),
+    "d4b_mg_pc_apply_host": (C.c_int, [_P, _P, _P]),
+    "d4b_mg_fcg_solve_host": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_double)]),
     "d4b_mg_fcg_solve": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_double), _P, _P]),
 }
 

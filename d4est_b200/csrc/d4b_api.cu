@@ -22,7 +22,32 @@ size_t d4b_generic_smem_bytes(int NX, int NQX);
 int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st, int *handled);
 int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_t> &cand, std::vector<int32_t> &rest);
 
+/* run-time switches of the host pipeline: defaults from the environment (read ONCE), changed by d4b_set_option */
+static struct { bool init; int no_late_pass, no_pipeline, pipe_trace, pipe_chunks; } g_opt;
+static void opts_init()
+{
+  if (g_opt.init) return;
+  g_opt.no_late_pass = getenv("D4B_NO_LATE_PASS") != nullptr; g_opt.no_pipeline = getenv("D4B_NO_PIPELINE") != nullptr;
+  g_opt.pipe_trace = getenv("D4B_PIPE_TRACE") != nullptr;
+  g_opt.pipe_chunks = getenv("D4B_PIPE_CHUNKS") ? atoi(getenv("D4B_PIPE_CHUNKS")) : 0;
+  g_opt.init = true;
+}
+extern int g_fcg_textbook;   /* d4b_solver.cu */
+
 extern "C" {
+
+int d4b_set_option(const char *name, int value)
+{
+  opts_init();
+  if (!name) { d4b_set_error("option name is NULL"); return D4B_EINVAL; }
+  if (!strcmp(name, "fcg_textbook_update")) g_fcg_textbook = value;
+  else if (!strcmp(name, "no_late_pass")) g_opt.no_late_pass = value;
+  else if (!strcmp(name, "no_pipeline")) g_opt.no_pipeline = value;
+  else if (!strcmp(name, "pipe_trace")) g_opt.pipe_trace = value;
+  else if (!strcmp(name, "pipe_chunks")) g_opt.pipe_chunks = value;
+  else { d4b_set_error("unknown option %s", name); return D4B_EINVAL; }
+  return D4B_OK;
+}
 
 const char *d4b_last_error(void) { return g_err; }
 const char *d4b_version(void) { return "d4est_b200 0.1 (sm_100a)"; }
@@ -166,9 +191,10 @@ int d4b_mesh_create(const d4b_mesh_desc_t *D, d4b_mesh_t **out)
   UP(G, D->G, 6 * m->total_quad) UP(hm_begin, D->hm_begin, nl + 1) UP(hm, D->hm, m->n_hm)
   UP(fac, D->fac, m->n_fac) UP(bc_g, D->bc_g, m->n_bc_g)
 #undef UP
-  D4B_CUDA(cudaMalloc((void **)&m->u_ghost, (m->ghost_nodes ? m->ghost_nodes : 1) * sizeof(double)));
-  D4B_CUDA(cudaMemset(m->u_ghost, 0, (m->ghost_nodes ? m->ghost_nodes : 1) * sizeof(double)));
-  D4B_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+#define D4B_CUDA_M(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { d4b_set_error("%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); d4b_mesh_destroy(m); return D4B_ECUDA; } } while (0)
+  D4B_CUDA_M(cudaMalloc((void **)&m->u_ghost, (m->ghost_nodes ? m->ghost_nodes : 1) * sizeof(double)));
+  D4B_CUDA_M(cudaMemset(m->u_ghost, 0, (m->ghost_nodes ? m->ghost_nodes : 1) * sizeof(double)));
+  D4B_CUDA_M(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
   /* halo lists */
   m->n_peers = D->n_peers;
   if (D->n_peers > 0) {
@@ -193,7 +219,7 @@ int d4b_mesh_create(const d4b_mesh_desc_t *D, d4b_mesh_t **out)
     int64_t dummy = 0;
     if ((rc = upload(&m->send_elem, D->send_elem, (size_t)D->send_begin[np], &dummy)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
     if ((rc = upload(&m->send_off, soff.data(), (size_t)D->send_begin[np], &dummy)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
-    D4B_CUDA(cudaMalloc((void **)&m->send_buf, (sn ? sn : 1) * sizeof(double)));
+    D4B_CUDA_M(cudaMalloc((void **)&m->send_buf, (sn ? sn : 1) * sizeof(double)));
   }
   if ((rc = d4b_fast_classify(m, D)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
   if ((rc = d4b_mesh_make_streams(m)) != D4B_OK) { d4b_mesh_destroy(m); return rc; }
@@ -206,7 +232,7 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   if (!m) return;
   cudaFree(m->deg); cudaFree(m->node_off); cudaFree(m->degq); cudaFree(m->quad_off); cudaFree(m->G);
   cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost);
-  cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
+  cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->host_work); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
   for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); cudaFree(m->fast[i].nrec); cudaFree(m->fast[i].v3_slots); }
   for (int i = 0; i < m->n_hp; i++) { cudaFree(m->hp[i].slots); cudaFree(m->hp[i].recs); }
   cudaFree(m->generic_list);
@@ -236,14 +262,27 @@ int d4b_mesh_kernel_split(const d4b_mesh_t *m, int64_t counts[3])
 int d4b_set_ghost_host(d4b_mesh_t *m, const double *ug)
 {
   if (m->ghost_nodes) D4B_CUDA(cudaMemcpy(m->u_ghost, ug, m->ghost_nodes * sizeof(double), cudaMemcpyHostToDevice));
+  m->ghost_supplied = 1;
   return D4B_OK;
+}
+
+/* The reference always exchanges ghosts inside the apply (dGMath/d4est_laplacian_with_opt.c:327).  A level with
+ * neighbour ranks therefore needs the NCCL communicator; without it the apply fails loudly instead of using a
+ * stale halo -- unless the caller supplied the ghost values itself (d4b_set_ghost_host). */
+static int d4b_halo_for_apply(d4b_mesh_t *m, const double *u, void *stream)
+{
+  if (m->n_peers == 0) return D4B_OK;
+  if (d4b_comm_size() > 1) return d4b_halo_exchange(m, u, stream);
+  if (m->ghost_supplied) return D4B_OK;
+  d4b_set_error("level has %d neighbour ranks but neither d4b_comm_init nor d4b_set_ghost_host was called: the halo of u is undefined", m->n_peers);
+  return D4B_ENCCL;
 }
 
 int d4b_apply_dev(d4b_mesh_t *m, const double *u, double *Au, void *stream)
 {
   cudaStream_t st = (cudaStream_t)stream;
   int handled = 0, rc;
-  if (m->n_peers > 0 && d4b_comm_size() > 1 && (rc = d4b_halo_exchange(m, u, stream)) != D4B_OK) return rc;
+  if ((rc = d4b_halo_for_apply(m, u, stream)) != D4B_OK) return rc;
   rc = d4b_launch_fast(m, u, Au, st, &handled);
   if (rc != D4B_OK) return rc;
   return rc;
@@ -263,7 +302,10 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
    * being full duplex, the remaining uploads.  Every element writes only its own nodes of Au. */
   /* can the kernel store straight into the caller's buffer (pinned, device-mapped host memory)? */
   double *Au_map = nullptr;
-  if (!getenv("D4B_NO_LATE_PASS")) {
+  opts_init();
+  const bool env_no_late = g_opt.no_late_pass, env_no_pipe = g_opt.no_pipeline, env_trace = g_opt.pipe_trace;
+  const int env_chunks = g_opt.pipe_chunks;
+  if (!env_no_late) {
     cudaPointerAttributes pa;
     if (cudaPointerGetAttributes(&pa, Au_host) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer)
       Au_map = static_cast<double *>(pa.devicePointer);
@@ -274,10 +316,10 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
    * after the halo exchange, which follows the last upload */
   if (m->n_fast == 1 && m->n_generic == 0 && m->fast[0].count == m->n_local && m->fast[0].nrec &&
       (m->n_peers == 0 || Au_map) &&
-      d4b_v3_supported(m->fast[0].N, m->fast[0].Nq) && m->n_local >= 8192 && !getenv("D4B_NO_PIPELINE")) {
+      d4b_v3_supported(m->fast[0].N, m->fast[0].Nq) && m->n_local >= 8192 && !env_no_pipe) {
     const d4b_fast_bucket &b = m->fast[0];
     int NCH = 16;
-    if (const char *e = getenv("D4B_PIPE_CHUNKS")) { int v = atoi(e); if (v >= 2 && v <= D4B_PIPE_MAX) NCH = v; }
+    if (env_chunks >= 2 && env_chunks <= D4B_PIPE_MAX) NCH = env_chunks;
     const int64_t N3 = (int64_t)b.N * b.N * b.N;
     int rc0;
     if (!m->copy_stream) {
@@ -311,7 +353,7 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
      * last chunk it reads. */
     if (m->pipe_late.count == 0) Au_map = nullptr;
     const bool defer = Au_map != nullptr || m->pipe_late.count == 0;
-    const bool trace = getenv("D4B_PIPE_TRACE") != nullptr;
+    const bool trace = env_trace;
     cudaEvent_t tv[5];
     if (trace) { for (int i = 0; i < 5; i++) cudaEventCreate(&tv[i]); cudaEventRecord(tv[0], m->in_stream); }
     for (int k = 0; k < nr; k++) {
@@ -335,6 +377,10 @@ int d4b_apply_host(d4b_mesh_t *m, const double *u_host, double *Au_host)
     }
     if (trace) { cudaEventRecord(tv[2], m->stream); cudaEventRecord(tv[3], m->copy_stream); }
     const bool dist = m->n_peers > 0 && d4b_comm_size() > 1;
+    if (m->n_peers > 0 && !dist && !m->ghost_supplied) {
+      d4b_set_error("level has %d neighbour ranks but neither d4b_comm_init nor d4b_set_ghost_host was called", m->n_peers);
+      return D4B_ENCCL;
+    }
     if (Au_map || dist) {
       if (waited < nr - 1) D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_in[nr - 1], 0));
       if (dist && (rc0 = d4b_halo_exchange(m, m->u_stage, m->stream)) != D4B_OK) return rc0;

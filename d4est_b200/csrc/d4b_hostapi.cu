@@ -1,0 +1,64 @@
+/* d4b_hostapi.cu -- entry points that take HOST vectors at the granularity d4est's solver stack calls them:
+ * one residual, one smoother call (cg_eigs + Chebyshev sweep), one bottom solve, one V-cycle preconditioner
+ * application.  Each stages its vectors once (H2D before, D2H after) around MANY operator applies, which is
+ * where the host boundary belongs: a smoother call is 15 + 15 + 1 applies for two uploads and two downloads.
+ * Used by the d4est-facing glue (d4est_b200/glue/d4est_b200_solver_glue.c). */
+#include "d4b_internal.h"
+#include <cstdlib>
+
+static int ensure_host_work(d4b_mesh *m)
+{
+  if (m->host_work) return D4B_OK;
+  D4B_CUDA(cudaMalloc((void **)&m->host_work, (size_t)(6 * (m->local_nodes + 2)) * sizeof(double)));
+  return D4B_OK;
+}
+
+extern "C" {
+
+/* r = rhs - A u on device vectors: the body of every build_residual callback of the Laplacian problems
+ * (e.g. Problems/Poisson/poisson_sinx_fcns.h:133-148: apply_lhs, then Au = rhs - Au) */
+int d4b_residual_dev(d4b_mesh_t *m, const double *u, const double *rhs, double *r, void *stream)
+{
+  int rc = d4b_apply_dev(m, u, r, stream);
+  if (rc != D4B_OK) return rc;
+  return d4b_vec_axpyeqz(m->local_nodes, -1., r, rhs, r, stream);
+}
+
+int d4b_residual_host(d4b_mesh_t *m, const double *u_host, const double *rhs_host, double *r_host)
+{
+  int rc = ensure_host_work(m); if (rc) return rc;
+  const int64_t n = m->local_nodes; const size_t nb = (size_t)n * sizeof(double);
+  double *u = m->host_work, *rhs = u + n, *r = rhs + n;
+  D4B_CUDA(cudaMemcpyAsync(u, u_host, nb, cudaMemcpyHostToDevice, m->stream));
+  D4B_CUDA(cudaMemcpyAsync(rhs, rhs_host, nb, cudaMemcpyHostToDevice, m->stream));
+  if ((rc = d4b_residual_dev(m, u, rhs, r, m->stream)) != D4B_OK) return rc;
+  D4B_CUDA(cudaMemcpyAsync(r_host, r, nb, cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  return D4B_OK;
+}
+
+/* One call of the reference's Chebyshev smoother on host vectors (d4est_solver_multigrid_smoother_cheby,
+ * Solver/d4est_solver_multigrid_smoother_cheby.c:264-360): optional cg_eigs (which also advances u, cg_eigs.c:230),
+ * *eig *= max_multiplier, then cheby_imax sweeps with [eig / ratio, eig]; on return u is smoothed and
+ * r = rhs - A u.  The bottom solver (bottom_solver_cheby.c:59-113) is the same call with compute_eig = 1. */
+int d4b_cheby_smooth_host(d4b_mesh_t *m, double *u_host, const double *rhs_host, double *r_host, int cheby_imax,
+                          int eigs_cg_imax, double lmax_lmin_ratio, double max_multiplier, int use_new_cg_eigs,
+                          int compute_eig, double *eig)
+{
+  int rc = ensure_host_work(m); if (rc) return rc;
+  const int64_t n = m->local_nodes; const size_t nb = (size_t)n * sizeof(double);
+  double *u = m->host_work, *rhs = u + n, *r = rhs + n, *work = r + n;
+  D4B_CUDA(cudaMemcpyAsync(u, u_host, nb, cudaMemcpyHostToDevice, m->stream));
+  D4B_CUDA(cudaMemcpyAsync(rhs, rhs_host, nb, cudaMemcpyHostToDevice, m->stream));
+  if (compute_eig) {
+    if ((rc = d4b_cg_eigs(m, u, rhs, eigs_cg_imax, use_new_cg_eigs, eig, work, m->stream)) != D4B_OK) return rc;
+    *eig *= max_multiplier;
+  }
+  if ((rc = d4b_cheby_iterate(m, u, rhs, r, cheby_imax, *eig / lmax_lmin_ratio, *eig, 1, work, m->stream)) != D4B_OK) return rc;
+  D4B_CUDA(cudaMemcpyAsync(u_host, u, nb, cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaMemcpyAsync(r_host, r, nb, cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  return D4B_OK;
+}
+
+} /* extern C */

@@ -45,7 +45,9 @@ struct d4b_mesh {
   int32_t *deg; int64_t *node_off; int32_t *degq; int64_t *quad_off;
   double *G; int32_t *hm_begin; d4b_hm_t *hm; double *fac; double *bc_g;
   double *u_ghost;                 /* [ghost_nodes] received halo                        */
+  int ghost_supplied;              /* d4b_set_ghost_host was called (single-process tests of the N > 1 layout) */
   double *u_stage, *Au_stage;      /* staging for d4b_apply_host                         */
+  double *host_work;               /* 6 n doubles: staging + work of the host-vector solver entry points */
   int64_t bytes, alg_bytes;
   size_t generic_smem;
   /* halo lists */

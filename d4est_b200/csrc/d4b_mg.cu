@@ -116,6 +116,7 @@ struct d4b_mg {
   double *u, *rhs, *r;       /* per-level stacked work vectors for levels < finest */
   int64_t *off;              /* offset of level l inside the stacks */
   double *work;              /* 3 * max nodes */
+  double *hbuf;              /* 8 * finest nodes: staging + FCG work of the host-vector entry points (lazy) */
   int vcycles_done;
 };
 
@@ -191,7 +192,7 @@ int d4b_mg_create(int n_levels, d4b_mesh_t **levels, d4b_mg_transfer_t **transfe
 void d4b_mg_destroy(d4b_mg_t *g)
 {
   if (!g) return;
-  cudaFree(g->u); cudaFree(g->rhs); cudaFree(g->r); cudaFree(g->work);
+  cudaFree(g->u); cudaFree(g->rhs); cudaFree(g->r); cudaFree(g->work); cudaFree(g->hbuf);
   free(g->lvl); free(g->tr); free(g->off); free(g->eigs); free(g);
 }
 int d4b_mg_get_eigs(d4b_mg_t *g, double *eigs) { memcpy(eigs, g->eigs, g->n_levels * sizeof(double)); return D4B_OK; }
@@ -273,10 +274,9 @@ int d4b_mg_solve(d4b_mg_t *g, double *u, const double *rhs, int *vcycles, double
   r2_last = r2; g->vcycles_done = 0;
   const double stoptol = g->par.vcycle_rtol * g->par.vcycle_rtol * r2 + g->par.vcycle_atol * g->par.vcycle_atol;
   while (g->vcycles_done < g->par.vcycle_imax && r2 > stoptol) {
-    if ((rc = d4b_mg_vcycle(g, u, rhs, nullptr, stream))) return rc;
-    if ((rc = d4b_apply_dev(g->lvl[top], u, Au, stream))) return rc;
-    if ((rc = d4b_vec_axpyeqz(n, -1., Au, rhs, r, stream))) return rc;
-    if ((rc = d4b_vec_dot(n, r, r, &r2, stream))) return rc;
+    /* the residual after a V-cycle is the one its last smoother call left behind (multigrid.c:1315,
+     * d4est_solver_multigrid_compute_residual outside the START state): no extra apply */
+    if ((rc = d4b_mg_vcycle(g, u, rhs, &r2, stream))) return rc;
     g->vcycles_done++;
     if (sqrt(r2 / r2_last) >= .99) break;
     r2_last = r2;
@@ -301,5 +301,43 @@ int d4b_mg_fcg_solve(d4b_mg_t *g, double *u, const double *rhs, int imax, double
 {
   return d4b_fcg_solve(g->lvl[g->n_levels - 1], u, rhs, imax, atol, rtol, d4b_mg_pc_apply, g, iters, final_res, work_6n, stream);
 }
+
+
+/* Host-vector forms: what d4est_krylov_pc_t.pc_apply (Solver/d4est_krylov_pc.h:13-33) and
+ * d4est_solver_fcg_solve (Solver/d4est_solver_fcg_improved.c:97) hand over are host arrays; one upload and one
+ * download bracket a whole V-cycle / a whole solve. */
+static int mg_hbuf(d4b_mg *g)
+{
+  if (g->hbuf) return D4B_OK;
+  D4B_CUDA(cudaMalloc((void **)&g->hbuf, (size_t)(8 * (g->lvl[g->n_levels - 1]->local_nodes + 2)) * sizeof(double)));
+  return D4B_OK;
+}
+int d4b_mg_pc_apply_host(d4b_mg_t *g, const double *r_host, double *z_host)
+{
+  int rc = mg_hbuf(g); if (rc) return rc;
+  d4b_mesh *top = g->lvl[g->n_levels - 1];
+  const int64_t n = top->local_nodes; const size_t nb = (size_t)n * sizeof(double);
+  double *r = g->hbuf, *z = r + n;
+  D4B_CUDA(cudaMemcpyAsync(r, r_host, nb, cudaMemcpyHostToDevice, top->stream));
+  if ((rc = d4b_mg_pc_apply(g, r, z, top->stream)) != D4B_OK) return rc;
+  D4B_CUDA(cudaMemcpyAsync(z_host, z, nb, cudaMemcpyDeviceToHost, top->stream));
+  D4B_CUDA(cudaStreamSynchronize(top->stream));
+  return D4B_OK;
+}
+int d4b_mg_fcg_solve_host(d4b_mg_t *g, double *u_host, const double *rhs_host, int imax, double atol, double rtol,
+                          int *iters, double *final_res)
+{
+  int rc = mg_hbuf(g); if (rc) return rc;
+  d4b_mesh *top = g->lvl[g->n_levels - 1];
+  const int64_t n = top->local_nodes; const size_t nb = (size_t)n * sizeof(double);
+  double *u = g->hbuf, *rhs = u + n, *work = rhs + n;
+  D4B_CUDA(cudaMemcpyAsync(u, u_host, nb, cudaMemcpyHostToDevice, top->stream));
+  D4B_CUDA(cudaMemcpyAsync(rhs, rhs_host, nb, cudaMemcpyHostToDevice, top->stream));
+  if ((rc = d4b_mg_fcg_solve(g, u, rhs, imax, atol, rtol, iters, final_res, work, top->stream)) != D4B_OK) return rc;
+  D4B_CUDA(cudaMemcpyAsync(u_host, u, nb, cudaMemcpyDeviceToHost, top->stream));
+  D4B_CUDA(cudaStreamSynchronize(top->stream));
+  return D4B_OK;
+}
+int d4b_mg_num_levels(const d4b_mg_t *g) { return g->n_levels; }
 
 } /* extern C */

@@ -5,7 +5,8 @@
  * hp-prolong :944-993; nodes/weights tables fetched :727-829), but built from
  * closed forms (Newton on Legendre polynomials + barycentric Lagrange) instead of
  * Vandermonde inverses through LAPACK, so no BLAS/LAPACK dependency exists on the
- * product side.  tests/test_ops.py checks them against the reference's tables.
+ * product side.  tests/test_oracle.py::test_product_1d_tables_match_the_reference_tables checks
+ * them against the reference's own tables (tests/golden/ref_ops_tables.fix, dumped by oracle/_ref/d4b_ops_dump).
  */
 #include "d4b_ops.h"
 #include <math.h>

@@ -8,6 +8,7 @@
 #include "d4b_internal.h"
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 
 #define VB 256
 static inline int vgrid(int64_t n) { int64_t g = (n + VB * 4 - 1) / (VB * 4); return (int)(g < 1 ? 1 : (g > 148 * 16 ? 148 * 16 : g)); }
@@ -16,8 +17,12 @@ __global__ void k_axpy(int64_t n, double a, const double *__restrict__ x, double
 { for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) y[i] = fma(a, x[i], y[i]); }
 __global__ void k_xpby(int64_t n, const double *__restrict__ x, double b, double *__restrict__ y)
 { for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) y[i] = fma(b, y[i], x[i]); }
-__global__ void k_axpyeqz(int64_t n, double a, const double *__restrict__ x, const double *__restrict__ y, double *z)
+/* z may alias x or y (each thread reads its element before it writes it): no __restrict__ here */
+__global__ void k_axpyeqz(int64_t n, double a, const double *x, const double *y, double *z)
 { for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) z[i] = fma(a, x[i], y[i]); }
+__global__ void k_scaleto2(int64_t n, double a, const double *__restrict__ x1, double *__restrict__ z1,
+                           const double *__restrict__ x2, double *__restrict__ z2)
+{ for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) { z1[i] = a * x1[i]; z2[i] = a * x2[i]; } }
 __global__ void k_scale(int64_t n, double a, double *__restrict__ x)
 { for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) x[i] *= a; }
 /* fused Chebyshev update (smoother_cheby.c:139-153): p = alpha (rhs - Au) + beta p;  u += p */
@@ -219,10 +224,20 @@ int d4b_cg_solve(d4b_mesh_t *m, double *u, const double *rhs, int imax, double a
   return D4B_OK;
 }
 
+} /* extern C */
+int g_fcg_textbook = 0;   /* d4b_set_option("fcg_textbook_update", ...) in d4b_api.cu */
+extern "C" {
+
 /* Flexible CG with a preconditioner callback on DEVICE vectors: restates d4est_solver_fcg_solve
  * (Solver/d4est_solver_fcg_improved.c:97-346); pc(ctx, r, z) plays d4est_krylov_pc_t.pc_apply
  * (Solver/d4est_krylov_pc.h:27-50); pc == NULL copies r (do_not_use_preconditioner).
- * The 2-4 dots of one iteration travel in ONE reduction (:245).  work: 6 n doubles. */
+ * The 2-4 dots of one iteration travel in ONE reduction (:245).  work: 6 n doubles.
+ * Direction update: the reference calls d4est_linalg_vec_axpyeqz(-gamma/rho, d, v, d) (:262; :266 for q), and
+ * that routine copies its third argument into the output BEFORE adding a*x (LinearAlgebra/d4est_linalg.c:217-221),
+ * so with the output aliasing x the old direction is gone by the time it is used: what the reference computes is
+ * d_k = (1 - gamma/rho) v_k, q_k = (1 - gamma/rho) w_k.  The iteration counts of the reference (the +-1 contract
+ * of north_star) come from that arithmetic, so it is the default here; d4b_set_option("fcg_textbook_update", 1)
+ * selects the update the source comments describe (d_k = v_k - gamma/rho d_{k-1}). */
 int d4b_fcg_solve(d4b_mesh_t *m, double *u, const double *rhs, int imax, double atol, double rtol,
                   int (*pc)(void *ctx, const double *r_dev, double *z_dev, void *stream), void *pc_ctx,
                   int *iters, double *final_res, double *work, void *stream)
@@ -245,8 +260,12 @@ int d4b_fcg_solve(d4b_mesh_t *m, double *u, const double *rhs, int imax, double 
     const double alpha = g[0], beta = g[1];
     if (k > 0) {
       const double gamma = g[2];
-      k_axpyeqz<<<vgrid(n), VB, 0, ST>>>(n, -gamma / rho, d, v, d); LAUNCH1();
-      k_axpyeqz<<<vgrid(n), VB, 0, ST>>>(n, -gamma / rho, q, w, q); LAUNCH1();
+      if (g_fcg_textbook) {
+        k_axpyeqz<<<vgrid(n), VB, 0, ST>>>(n, -gamma / rho, d, v, d); LAUNCH1();
+        k_axpyeqz<<<vgrid(n), VB, 0, ST>>>(n, -gamma / rho, q, w, q); LAUNCH1();
+      } else {
+        k_scaleto2<<<vgrid(n), VB, 0, ST>>>(n, 1. - gamma / rho, v, d, w, q); LAUNCH1();
+      }
       rho = beta - (gamma * gamma) / rho;
     } else {
       rho = beta;

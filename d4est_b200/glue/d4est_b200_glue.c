@@ -5,6 +5,9 @@
 #include "d4est_b200_glue.h"
 #include "../csrc/d4b_ops.h"
 #include <d4est_mortars_with_opt.h>
+#include <d4est_laplacian_flux.h>
+#include <d4est_laplacian_flux_sipg.h>
+#include <d4est_xyz_functions.h>
 #include <d4est_laplacian_with_opt_flux_sipg.h>
 #include <d4est_lgl.h>
 #include <d4est_reference.h>
@@ -23,7 +26,10 @@ typedef struct {
 typedef struct {
   p4est_t *p4est;
   d4est_ghost_t *ghost;
-  d4est_laplacian_with_opt_flux_data_t *flux;
+  /* the three things the recording callbacks need from a flux-data struct; filled from
+   * d4est_laplacian_with_opt_flux_data_t or from the baseline twin's d4est_laplacian_flux_data_t */
+  d4est_laplacian_with_opt_flux_sipg_params_t *sp;   /* common leading fields of both sipg parameter structs */
+  d4est_laplacian_bc_t bc_type; void *bc_data;
   int n_local;
   rec_t *rec; size_t nrec, caprec;
   double *fac; size_t nfac, capfac;
@@ -90,8 +96,7 @@ static void check_tcode(d4est_operators_t *ops, int f_m, int f_p, int o, int tco
 static double penalty_sigma(recorder_t *R, d4est_element_data_t *em, d4est_element_data_t *ep,
                             int deg_m, double hm, int deg_p, double hp)
 { /* dGMath/d4est_laplacian_with_opt_flux_sipg.c:620-639 (interface), :75-86 (boundary) */
-  d4est_laplacian_with_opt_flux_sipg_params_t *sp =
-      (d4est_laplacian_with_opt_flux_sipg_params_t *)R->flux->flux_data;
+  d4est_laplacian_with_opt_flux_sipg_params_t *sp = R->sp;
   double mult = d4est_laplacian_with_opt_flux_sipg_get_multiplier(sp, em->region, ep->region);
   return mult * sp->sipg_penalty_fcn(deg_m, hm, deg_p, hp, sp->sipg_penalty_prefactor);
 }
@@ -192,10 +197,9 @@ static void record_boundary(p4est_t *p4est, d4est_element_data_t *e_m, int f_m,
                             d4est_mesh_data_t *factors, void *ctx)
 {
   recorder_t *R = (recorder_t *)ctx;
-  if (R->flux->bc_type != BC_DIRICHLET)
+  if (R->bc_type != BC_DIRICHLET)
     D4EST_ABORT("d4est_b200: only BC_DIRICHLET is implemented on the device path");
-  d4est_laplacian_with_opt_dirichlet_bc_t *bc =
-      (d4est_laplacian_with_opt_dirichlet_bc_t *)R->flux->bc_data;
+  d4est_laplacian_with_opt_dirichlet_bc_t *bc = (d4est_laplacian_with_opt_dirichlet_bc_t *)R->bc_data;
   int degq = e_m->deg_quad, nq = degq + 1, n2 = nq * nq;
   int nl2 = d4est_lgl_get_nodes(2, e_m->deg);
   size_t s0 = (size_t)factors->local_strides[e_m->id].mortar_quad_stride[f_m];
@@ -242,10 +246,35 @@ static void record_boundary(p4est_t *p4est, d4est_element_data_t *e_m, int f_m,
 }
 
 /* -------------------------------------------------------------------- flatten */
+static d4b_mesh_desc_t *flatten_impl(p4est_t *p4est, d4est_ghost_t *ghost, void *sipg_params,
+                                     d4est_laplacian_bc_t bc_type, void *bc_data, d4est_operators_t *ops,
+                                     d4est_geometry_t *geom, d4est_quadrature_t *quad, d4est_mesh_data_t *factors);
+
 d4b_mesh_desc_t *d4est_b200_flatten(p4est_t *p4est, d4est_ghost_t *ghost,
                                     d4est_laplacian_with_opt_flux_data_t *flux_data,
                                     d4est_operators_t *ops, d4est_geometry_t *geom,
                                     d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
+{
+  if (flux_data->flux_type != FLUX_SIPG) D4EST_ABORT("d4est_b200: only the SIPG flux is implemented");
+  return flatten_impl(p4est, ghost, flux_data->flux_data, flux_data->bc_type, flux_data->bc_data, ops, geom, quad, factors);
+}
+
+/* Same tables from the baseline twin's flux data (d4est_laplacian_flux_data_t, dGMath/d4est_laplacian_flux.h):
+ * its sipg parameter struct has the same leading fields (penalty prefactor, region multipliers, penalty function,
+ * dGMath/d4est_laplacian_flux_sipg.h:18-40 vs ..._with_opt_flux_sipg.h:18-40) and its Dirichlet struct the same
+ * three members.  The twin evaluates every interface twice and uses max(deg) for the mortar Lobatto space; the two
+ * variants agree to 1e-13 (Tests/Unit/d4est_test_laplacian_speedup.c:485), so one device path serves both. */
+d4b_mesh_desc_t *d4est_b200_flatten_baseline(p4est_t *p4est, d4est_ghost_t *ghost, d4est_laplacian_flux_data_t *fd,
+                                             d4est_operators_t *ops, d4est_geometry_t *geom,
+                                             d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
+{
+  if (fd->flux_type != FLUX_SIPG) D4EST_ABORT("d4est_b200: only the SIPG flux is implemented");
+  return flatten_impl(p4est, ghost, fd->flux_data, fd->bc_type, fd->bc_data, ops, geom, quad, factors);
+}
+
+static d4b_mesh_desc_t *flatten_impl(p4est_t *p4est, d4est_ghost_t *ghost, void *sipg_params,
+                                     d4est_laplacian_bc_t bc_type, void *bc_data, d4est_operators_t *ops,
+                                     d4est_geometry_t *geom, d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
 {
   int nl = (int)p4est->local_num_quadrants;
   int ng = (int)ghost->ghost->ghosts.elem_count;
@@ -305,7 +334,8 @@ d4b_mesh_desc_t *d4est_b200_flatten(p4est_t *p4est, d4est_ghost_t *ghost,
 
   /* faces: one walk of the reference iterator with recording callbacks */
   recorder_t R; memset(&R, 0, sizeof R);
-  R.p4est = p4est; R.ghost = ghost; R.flux = flux_data; R.n_local = nl; R.quad_type = D->quad_type;
+  R.p4est = p4est; R.ghost = ghost; R.n_local = nl; R.quad_type = D->quad_type;
+  R.sp = (d4est_laplacian_with_opt_flux_sipg_params_t *)sipg_params; R.bc_type = bc_type; R.bc_data = bc_data;
   d4est_mortars_with_opt_fcn_ptrs_t fp;
   fp.flux_interface_fcn = record_interface; fp.flux_boundary_fcn = record_boundary; fp.user_ctx = &R;
   d4est_mortars_with_opt_compute_flux_on_local_elements(p4est, ghost, ops, geom, quad, factors, &fp);
@@ -380,18 +410,18 @@ void d4est_b200_flatten_free(d4b_mesh_desc_t *D)
 #define D4B_GLUE_MAX_LEVELS 64
 static struct { d4est_mesh_data_t *key; d4b_mesh_t *mesh; } g_levels[D4B_GLUE_MAX_LEVELS];
 
-d4b_mesh_t *d4est_b200_level_get(p4est_t *p4est, d4est_ghost_t *ghost,
-                                 d4est_laplacian_with_opt_flux_data_t *flux_data,
-                                 d4est_operators_t *ops, d4est_geometry_t *geom,
-                                 d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
+static d4b_mesh_t *level_lookup(d4est_mesh_data_t *factors, int *free_slot)
 {
-  int slot = -1;
+  *free_slot = -1;
   for (int i = 0; i < D4B_GLUE_MAX_LEVELS; i++) {
     if (g_levels[i].key == factors) return g_levels[i].mesh;
-    if (slot < 0 && !g_levels[i].key) slot = i;
+    if (*free_slot < 0 && !g_levels[i].key) *free_slot = i;
   }
-  if (slot < 0) D4EST_ABORT("d4est_b200: too many resident levels");
-  d4b_mesh_desc_t *D = d4est_b200_flatten(p4est, ghost, flux_data, ops, geom, quad, factors);
+  if (*free_slot < 0) D4EST_ABORT("d4est_b200: too many resident levels");
+  return NULL;
+}
+static d4b_mesh_t *level_store(int slot, d4est_mesh_data_t *factors, d4b_mesh_desc_t *D)
+{
   d4b_mesh_t *m = NULL;
   if (d4b_mesh_create(D, &m) != D4B_OK) {
     fprintf(stderr, "d4est_b200: %s\n", d4b_last_error());
@@ -400,6 +430,25 @@ d4b_mesh_t *d4est_b200_level_get(p4est_t *p4est, d4est_ghost_t *ghost,
   d4est_b200_flatten_free(D);
   g_levels[slot].key = factors; g_levels[slot].mesh = m;
   return m;
+}
+
+d4b_mesh_t *d4est_b200_level_get(p4est_t *p4est, d4est_ghost_t *ghost,
+                                 d4est_laplacian_with_opt_flux_data_t *flux_data,
+                                 d4est_operators_t *ops, d4est_geometry_t *geom,
+                                 d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
+{
+  int slot; d4b_mesh_t *m = level_lookup(factors, &slot);
+  if (m) return m;
+  return level_store(slot, factors, d4est_b200_flatten(p4est, ghost, flux_data, ops, geom, quad, factors));
+}
+
+d4b_mesh_t *d4est_b200_level_get_baseline(p4est_t *p4est, d4est_ghost_t *ghost, d4est_laplacian_flux_data_t *fd,
+                                          d4est_operators_t *ops, d4est_geometry_t *geom,
+                                          d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
+{
+  int slot; d4b_mesh_t *m = level_lookup(factors, &slot);
+  if (m) return m;
+  return level_store(slot, factors, d4est_b200_flatten_baseline(p4est, ghost, fd, ops, geom, quad, factors));
 }
 
 void d4est_b200_level_invalidate(d4est_mesh_data_t *factors)
@@ -413,6 +462,14 @@ void d4est_b200_level_invalidate_all(void)
     if (g_levels[i].key) { d4b_mesh_destroy(g_levels[i].mesh); g_levels[i].key = NULL; g_levels[i].mesh = NULL; }
 }
 
+static void check_rc(int rc, const char *what)
+{
+  if (rc == D4B_OK) return;
+  fprintf(stderr, "d4est_b200: %s: %s\n", what, d4b_last_error());
+  D4EST_ABORT("d4est_b200: device call failed (no CPU fallback)");
+}
+
+/* ---------------------------------------------------------------- operator entry points */
 void d4est_b200_laplacian_apply_aij(p4est_t *p4est, d4est_ghost_t *ghost,
                                     d4est_ghost_data_t *ghost_data, d4est_elliptic_data_t *vecs,
                                     d4est_laplacian_with_opt_flux_data_t *flux_data,
@@ -422,9 +479,81 @@ void d4est_b200_laplacian_apply_aij(p4est_t *p4est, d4est_ghost_t *ghost,
 {
   d4b_mesh_t *m = d4est_b200_level_get(p4est, ghost, flux_data, ops, geom, quad, factors);
   size_t off = (size_t)which_field * (size_t)vecs->local_nodes; /* …_with_opt.c:199 */
-  if (d4b_apply_host(m, vecs->u + off, vecs->Au + off) != D4B_OK) {
-    fprintf(stderr, "d4est_b200: %s\n", d4b_last_error());
-    D4EST_ABORT("d4est_b200: device apply failed (no CPU fallback)");
-  }
+  check_rc(d4b_apply_host(m, vecs->u + off, vecs->Au + off), "apply");
   (void)ghost_data;
+}
+
+/* behind the baseline twin d4est_laplacian_apply_aij (dGMath/d4est_laplacian.c:317), same argument list */
+void d4est_b200_laplacian_baseline_apply_aij(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost_data_t *ghost_data,
+                                             d4est_elliptic_data_t *vecs, d4est_laplacian_flux_data_t *flux_fcn_data,
+                                             d4est_operators_t *ops, d4est_geometry_t *geom, d4est_quadrature_t *quad,
+                                             d4est_mesh_data_t *factors, int which_field)
+{
+  d4b_mesh_t *m = d4est_b200_level_get_baseline(p4est, ghost, flux_fcn_data, ops, geom, quad, factors);
+  size_t off = (size_t)which_field * (size_t)vecs->local_nodes;
+  check_rc(d4b_apply_host(m, vecs->u + off, vecs->Au + off), "apply (baseline twin)");
+  (void)ghost_data;
+}
+
+/* d4est_apply_operator_fcn_t (EllipticSystem/d4est_elliptic_eqns.h:12-24): install as prob_fcns.apply_lhs with
+ * prob_fcns.user = the d4est_laplacian_with_opt_flux_data_t* of the problem */
+void d4est_b200_apply_lhs(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost_data_t *ghost_data,
+                          d4est_elliptic_data_t *vecs, d4est_operators_t *ops, d4est_geometry_t *geom,
+                          d4est_quadrature_t *quad, d4est_mesh_data_t *factors, void *user)
+{
+  d4est_b200_laplacian_apply_aij(p4est, ghost, ghost_data, vecs, (d4est_laplacian_with_opt_flux_data_t *)user, ops,
+                                 geom, quad, factors, 0);
+}
+
+/* d4est_apply_operator_fcn_t for prob_fcns.build_residual (:32): Au = rhs - A u, the body of the Laplacian
+ * problems' build_residual callbacks (Problems/Poisson/poisson_sinx_fcns.h:133-148), one upload of u and rhs */
+void d4est_b200_build_residual(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost_data_t *ghost_data,
+                               d4est_elliptic_data_t *vecs, d4est_operators_t *ops, d4est_geometry_t *geom,
+                               d4est_quadrature_t *quad, d4est_mesh_data_t *factors, void *user)
+{
+  d4b_mesh_t *m = d4est_b200_level_get(p4est, ghost, (d4est_laplacian_with_opt_flux_data_t *)user, ops, geom, quad, factors);
+  check_rc(d4b_residual_host(m, vecs->u, vecs->rhs, vecs->Au), "build_residual");
+  (void)ghost_data;
+}
+
+/* d4est_laplacian_build_rhs_with_strong_bc (dGMath/d4est_laplacian.c:16-134), same argument list:
+ * rhs = M f - A(u = 0), the second term carrying the inhomogeneous Dirichlet data.  A(0) runs on the device; the
+ * mass-matrix product with the source term stays the reference's own host code (setup, once per solve). */
+void d4est_b200_laplacian_build_rhs_with_strong_bc(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost_data_t *ghost_data,
+                                                   d4est_operators_t *ops, d4est_geometry_t *geom,
+                                                   d4est_quadrature_t *quad, d4est_mesh_data_t *factors,
+                                                   d4est_elliptic_data_t *prob_vecs,
+                                                   d4est_laplacian_flux_data_t *flux_fcn_data_for_build_rhs,
+                                                   double *rhs, d4est_xyz_fcn_t problem_rhs_fcn,
+                                                   d4est_mesh_init_field_option_t init_option, void *ctx, int which_field)
+{
+  int n = prob_vecs->local_nodes;
+  double *u0 = P4EST_ALLOC_ZERO(double, n), *Au0 = P4EST_ALLOC_ZERO(double, n);
+  /* the boundary data belongs to THIS flux struct: flatten it separately from the (homogeneous) operator level */
+  d4b_mesh_desc_t *D = d4est_b200_flatten_baseline(p4est, ghost, flux_fcn_data_for_build_rhs, ops, geom, quad, factors);
+  d4b_mesh_t *m = NULL;
+  check_rc(d4b_mesh_create(D, &m), "build_rhs level");
+  d4est_b200_flatten_free(D);
+  check_rc(d4b_apply_host(m, u0, Au0), "build_rhs apply");
+  d4b_mesh_destroy(m);
+  double *f = P4EST_ALLOC(double, init_option == INIT_FIELD_ON_LOBATTO ? n : d4est_mesh_get_local_quad_nodes(p4est));
+  d4est_mesh_init_field(p4est, f, problem_rhs_fcn, ops, geom, factors, init_option, ctx);
+  for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+    sc_array_t *tq = &p4est_tree_array_index(p4est->trees, tt)->quadrants;
+    for (size_t q = 0; q < tq->elem_count; ++q) {
+      d4est_element_data_t *ed = (d4est_element_data_t *)p4est_quadrant_array_index(tq, q)->p.user_data;
+      d4est_quadrature_volume_t mo;
+      mo.dq = ed->dq; mo.tree = ed->tree; mo.q[0] = ed->q[0]; mo.q[1] = ed->q[1]; mo.q[2] = ed->q[2]; mo.element_id = ed->id;
+      double *J = d4est_mesh_get_jacobian_on_quadrature_points(factors, ed);
+      if (init_option == INIT_FIELD_ON_LOBATTO)
+        d4est_quadrature_apply_mass_matrix(ops, geom, quad, &mo, QUAD_OBJECT_VOLUME, QUAD_INTEGRAND_UNKNOWN,
+                                           &f[ed->nodal_stride], ed->deg, J, ed->deg_quad, &rhs[ed->nodal_stride]);
+      else
+        d4est_quadrature_apply_galerkin_integral(ops, geom, quad, &mo, QUAD_OBJECT_VOLUME, QUAD_INTEGRAND_UNKNOWN,
+                                                 &f[ed->quad_stride], ed->deg, J, ed->deg_quad, &rhs[ed->nodal_stride]);
+    }
+  }
+  for (int i = 0; i < n; i++) rhs[i] -= Au0[i];
+  P4EST_FREE(u0); P4EST_FREE(Au0); P4EST_FREE(f);
+  (void)ghost_data; (void)which_field;
 }

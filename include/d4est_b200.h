@@ -187,6 +187,11 @@ int d4b_cg_solve(d4b_mesh_t *m, double *u, const double *rhs, int imax, double a
 int d4b_fcg_solve(d4b_mesh_t *m, double *u, const double *rhs, int imax, double atol, double rtol,
                   d4b_pc_fcn_t pc, void *pc_ctx, int *iters, double *final_res, double *work_6n,
                   void *cuda_stream);
+/* options: "fcg_textbook_update" (default 0 = the arithmetic d4est_solver_fcg_solve really performs, see
+ * d4b_solver.cu; 1 = d_k = v_k - gamma/rho d_{k-1});  test switches of the d4b_apply_host pipeline, whose defaults
+ * come from the environment variables of the same name in capitals with a D4B_ prefix, read once:
+ * "no_pipeline", "no_late_pass", "pipe_trace", "pipe_chunks" */
+int d4b_set_option(const char *name, int value);
 
 /* ---- multigrid on cached levels.  Transfer table between two levels (one entry per COARSE
  *      element; d4est_solver_multigrid_refine_data_t{hrefine,degh[8],degH} Solver/d4est_solver_multigrid.h:12-18):
@@ -218,6 +223,24 @@ int d4b_mg_solve(d4b_mg_t *g, double *u_dev, const double *rhs_dev, int *vcycles
 int d4b_mg_pc_apply(void *mg, const double *r_dev, double *z_dev, void *cuda_stream);
 int d4b_mg_fcg_solve(d4b_mg_t *g, double *u_dev, const double *rhs_dev, int imax, double atol, double rtol,
                      int *iters, double *final_res, double *work_6n, void *cuda_stream);
+int d4b_mg_num_levels(const d4b_mg_t *g);
+
+/* ---- HOST-vector forms at the granularity d4est's solver stack calls them: one upload / download around MANY
+ *      applies (a smoother call is 15 + 15 + 1 of them).  These are what the d4est-facing glue
+ *      (include/d4est_b200_glue.h) installs behind d4est's own interfaces:
+ *      build_residual callbacks (EllipticSystem/d4est_elliptic_eqns.h:32; e.g. poisson_sinx_fcns.h:133-148),
+ *      d4est_solver_multigrid_smoother_t.smooth / _bottom_solver_t.solve (Solver/d4est_solver_multigrid.h:129-144;
+ *      bodies smoother_cheby.c:264-360, bottom_solver_cheby.c:59-113),
+ *      d4est_krylov_pc_t.pc_apply (Solver/d4est_krylov_pc.h:13-33; body d4est_krylov_pc_multigrid.c:41-75),
+ *      d4est_solver_fcg_solve (Solver/d4est_solver_fcg_improved.c:97). */
+int d4b_residual_dev(d4b_mesh_t *m, const double *u_dev, const double *rhs_dev, double *r_dev, void *cuda_stream);
+int d4b_residual_host(d4b_mesh_t *m, const double *u_host, const double *rhs_host, double *r_host);
+int d4b_cheby_smooth_host(d4b_mesh_t *m, double *u_host, const double *rhs_host, double *r_host, int cheby_imax,
+                          int eigs_cg_imax, double lmax_lmin_ratio, double max_multiplier, int use_new_cg_eigs,
+                          int compute_eig, double *eig);
+int d4b_mg_pc_apply_host(d4b_mg_t *g, const double *r_host, double *z_host);
+int d4b_mg_fcg_solve_host(d4b_mg_t *g, double *u_host, const double *rhs_host, int imax, double atol, double rtol,
+                          int *iters, double *final_res);
 
 #ifdef __cplusplus
 }

@@ -27,9 +27,15 @@ def load(path):
             count = int(np.frombuffer(f.read(8), dtype=np.int64)[0])
             dt = np.dtype(_DT[int(dtype)])
             out[nm.rstrip(b"\0").decode()] = np.frombuffer(f.read(count * dt.itemsize), dtype=dt).copy()
-    if "hm" in out:
-        out["hm"] = out["hm"].view(HM_DTYPE)
+    for k in list(out):
+        if k == "hm" or k.endswith(".hm"):
+            out[k] = out[k].view(HM_DTYPE)
     return out
+
+
+def sub(fx, prefix):
+    """The arrays of one level of a multigrid fixture ("L2." ...) as a plain level fixture."""
+    return {k[len(prefix):]: v for k, v in fx.items() if k.startswith(prefix)}
 
 
 def save(path, arrays):

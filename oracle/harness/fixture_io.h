@@ -18,10 +18,14 @@ static void fix_write(FILE *f, const char *name, int dtype, int64_t count, const
   fwrite(nm, 1, 32, f); fwrite(hdr, 4, 2, f); fwrite(&count, 8, 1, f);
   if (count > 0) fwrite(data, (size_t)fix_size[dtype], (size_t)count, f);
 }
+static const char *fix_prefix = "";   /* e.g. "L2." for level 2 of a multigrid fixture */
+static void fix_write_p(FILE *f, const char *name, int dtype, int64_t count, const void *data)
+{ char nm[64]; snprintf(nm, sizeof nm, "%s%s", fix_prefix, name); fix_write(f, nm, dtype, count, data); }
 static void fix_write_desc(FILE *f, const d4b_mesh_desc_t *D)
 {
   int32_t hdr[4] = { D->n_local, D->n_ghost, D->quad_type, D->n_peers };
   int64_t nh = D->hm_begin[D->n_local];
+#define fix_write fix_write_p
   fix_write(f, "hdr", FIX_I32, 4, hdr);
   fix_write(f, "deg", FIX_I32, D->n_local + D->n_ghost, D->deg);
   fix_write(f, "node_off", FIX_I64, D->n_local + D->n_ghost + 1, D->node_off);
@@ -36,5 +40,6 @@ static void fix_write_desc(FILE *f, const d4b_mesh_desc_t *D)
   fix_write(f, "send_begin", FIX_I32, D->n_peers + 1, D->send_begin);
   fix_write(f, "send_elem", FIX_I32, D->send_begin[D->n_peers], D->send_elem);
   fix_write(f, "recv_begin", FIX_I32, D->n_peers + 1, D->recv_begin);
+#undef fix_write
 }
 #endif

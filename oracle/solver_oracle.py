@@ -1,11 +1,16 @@
 """CPU restatement (numpy) of the solver pieces around the apply.  TEST INFRASTRUCTURE ONLY.
 
-PINNED for cg_eigs and the Chebyshev iteration against the unmodified reference (the fixtures hold
-sol_eig / sol_u_after_eigs / sol_u_after_cheby / sol_r_after_cheby written by oracle/_ref/d4b_harness
-calling the reference's cg_eigs and d4est_solver_multigrid_smoother_cheby_iterate_aux).  The flexible
-CG, plain CG and the V-cycle are restated from source ("parity unpinned" for those three: the
-reference's own drivers need PETSc headers / a live p4est hierarchy that the serial oracle build does
-not have; they are pinned only through their building blocks above).
+PARITY PINNED against the unmodified reference for every function (tests/test_oracle.py):
+  cg_eigs, cheby_iterate   fixtures hold sol_eig / sol_u_after_eigs / sol_u_after_cheby / sol_r_after_cheby written by
+                           oracle/_ref/d4b_harness calling the reference's cg_eigs and ..._smoother_cheby_iterate_aux
+  fcg_solve, cg_solve      the reference's d4est_solver_fcg_solve / d4est_solver_cg_solve run for a fixed 25
+                           iterations on the curved hp mesh (krylov_fcg25_u / krylov_cg25_u in the multigrid
+                           fixture written by oracle/_ref/d4b_mg_harness; the drivers compile against typedef-only
+                           PETSc/HDF5 headers, oracle/ref_build/include/)
+  transfer                 the reference's d4est_operators_apply_{p,hp}_prolong[_transpose] on probe vectors over
+                           the hierarchy captured from its own coarsening (T*.ref_restricted / T*.ref_prolonged)
+  mg_vcycle / mg_pc        the reference's d4est_krylov_pc_multigrid_apply = d4est_solver_multigrid_solve with one
+                           V-cycle: first preconditioner application of its MG-FCG solve (mg_r0 -> mg_z0)
 `A` is any callable u -> A u (normally lambda u: dg_oracle.apply(fx, u)).
 """
 import numpy as np
@@ -77,8 +82,13 @@ def cg_solve(A, u, rhs, imax, atol, rtol):
     return u, i, dn
 
 
-def fcg_solve(A, u, rhs, imax, atol, rtol, pc=None):
-    """Solver/d4est_solver_fcg_improved.c:97-346."""
+def fcg_solve(A, u, rhs, imax, atol, rtol, pc=None, textbook=False):
+    """Solver/d4est_solver_fcg_improved.c:97-346, INCLUDING what its direction update really computes:
+    d4est_linalg_vec_axpyeqz(a, x, y, z) copies y into z and then adds a*x (LinearAlgebra/d4est_linalg.c:217-221),
+    and the driver calls it with z aliasing x (:262 `axpyeqz(-gamma/rho, d, v, d)`, :266 same for q), so the old
+    direction is overwritten before it is used: d_k = (1 - gamma/rho) v_k, q_k = (1 - gamma/rho) w_k.  That is the
+    arithmetic the reference's iteration counts come from (pinned by krylov_fcg25_u); textbook=True gives the
+    update the comments in the source describe (d_k = v_k - gamma/rho d_{k-1})."""
     r = rhs - A(u)
     tol = atol + rtol * np.sqrt(r @ r)
     rho = None
@@ -89,8 +99,12 @@ def fcg_solve(A, u, rhs, imax, atol, rtol, pc=None):
         alpha, beta = v @ r, v @ w
         if k > 0:
             gamma, rr = v @ q, r @ r
-            d = -gamma / rho * d + v
-            q = -gamma / rho * q + w
+            if textbook:
+                d = -gamma / rho * d + v
+                q = -gamma / rho * q + w
+            else:
+                d = (1. - gamma / rho) * v
+                q = (1. - gamma / rho) * w
             rho = beta - gamma * gamma / rho
         else:
             rho, d, q = beta, v.copy(), w.copy()
@@ -135,3 +149,67 @@ def brick_transfer_table(n_coarse_per_dir, deg):
             "coarse_off": (np.arange(nH, dtype=np.int64) * N3),
             "child_deg": np.full(8 * nH, deg, np.int32),
             "child_off": (np.arange(8 * nH, dtype=np.int64) * N3)}
+
+
+def mg_params(pd):
+    """d4b_mg_params_t fields from the "mg_params" array of a multigrid fixture (order: d4b_mg_harness.c)."""
+    keys = ["vcycle_imax", "vcycle_rtol", "vcycle_atol", "cheby_imax", "cheby_eigs_cg_imax", "cheby_eigs_lmax_lmin_ratio",
+            "cheby_eigs_max_multiplier", "eigs_reuse_fromdownvcycle", "eigs_reuse_fromlastvcycle", "use_new_cg_eigs",
+            "bottom_kind", "bottom_imax", "bottom_eigs_cg_imax", "bottom_eigs_lmax_lmin_ratio",
+            "bottom_eigs_max_multiplier", "bottom_atol", "bottom_rtol", "fcg_atol", "fcg_rtol", "ref_seconds"]
+    ints = {"vcycle_imax", "cheby_imax", "cheby_eigs_cg_imax", "eigs_reuse_fromdownvcycle", "eigs_reuse_fromlastvcycle",
+            "use_new_cg_eigs", "bottom_kind", "bottom_imax", "bottom_eigs_cg_imax"}
+    return {k: (int(v) if k in ints else float(v)) for k, v in zip(keys, pd)}
+
+
+def mg_vcycle(A, tabs, sizes, u, rhs, par, eigs, vcycles_done=0):
+    """One V-cycle: Solver/d4est_solver_multigrid.c:751-1330.  A[l]: operator of level l (0 = coarsest),
+    tabs[l]: transfer table between l and l+1, sizes[l]: nodes of level l.  Smoother = cg_eigs (when the reuse
+    flags ask for it, ..._smoother_cheby.c:221-262, 264-360) + Chebyshev; bottom = ..._bottom_solver_cheby.c:59-113.
+    Returns (u, r_top)."""
+    top = len(A) - 1
+    us, fs, rs = [None] * (top + 1), [None] * (top + 1), [None] * (top + 1)
+    us[top], fs[top] = u, rhs
+
+    def smooth(l, down):
+        if down:
+            compute = not (par["eigs_reuse_fromlastvcycle"] and vcycles_done != 0)
+        else:
+            compute = not (par["eigs_reuse_fromdownvcycle"] or (par["eigs_reuse_fromlastvcycle"] and vcycles_done != 0))
+        if compute:
+            eigs[l], us[l] = cg_eigs(A[l], us[l], fs[l], par["cheby_eigs_cg_imax"], bool(par["use_new_cg_eigs"]))
+            eigs[l] *= par["cheby_eigs_max_multiplier"]
+        us[l], rs[l] = cheby_iterate(A[l], us[l], fs[l], par["cheby_imax"], eigs[l] / par["cheby_eigs_lmax_lmin_ratio"], eigs[l])
+
+    for l in range(top, 0, -1):
+        if l != top:
+            us[l] = np.zeros(sizes[l])
+        smooth(l, True)
+        fs[l - 1] = transfer(tabs[l - 1], rs[l], sizes[l - 1], True)
+    us[0] = np.zeros(sizes[0])
+    if par["bottom_kind"] == 1:
+        us[0], _, _ = cg_solve(A[0], us[0], fs[0], par["bottom_imax"], par["bottom_atol"], par["bottom_rtol"])
+    else:
+        e, us[0] = cg_eigs(A[0], us[0], fs[0], par["bottom_eigs_cg_imax"], bool(par["use_new_cg_eigs"]))
+        e *= par["bottom_eigs_max_multiplier"]; eigs[0] = e
+        us[0], rs[0] = cheby_iterate(A[0], us[0], fs[0], par["bottom_imax"], e / par["bottom_eigs_lmax_lmin_ratio"], e)
+    for l in range(top):
+        us[l + 1] = us[l + 1] + transfer(tabs[l], us[l], sizes[l + 1], False)
+        smooth(l + 1, False)
+    return us[top], rs[top]
+
+
+def mg_pc(A, tabs, sizes, r, par):
+    """z = MG(r) from a zero guess with vcycle_imax cycles: Solver/d4est_krylov_pc_multigrid.c:41-75 +
+    d4est_solver_multigrid_solve (multigrid.c:1420-1500)."""
+    z = np.zeros(sizes[-1]); eigs = [0.] * len(A)
+    r2 = r2_last = float(r @ r)
+    stop = par["vcycle_rtol"] ** 2 * r2 + par["vcycle_atol"] ** 2
+    done = 0
+    while done < par["vcycle_imax"] and r2 > stop:
+        z, rt = mg_vcycle(A, tabs, sizes, z, r, par, eigs, done)
+        r2 = float(rt @ rt); done += 1
+        if np.sqrt(r2 / r2_last) >= .99:
+            break
+        r2_last = r2
+    return z

@@ -53,23 +53,24 @@ def test_non_power_of_two_brick_is_spd_and_symmetric():
 
 def test_host_pipeline_equals_plain_host_path():
     """d4b_apply_host on a uniform level runs as a 3-stream pipeline over element ranges (chunked H2D, kernel per
-    range once the chunks it reads have arrived, D2H per finished range); D4B_NO_PIPELINE=1 is the plain
+    range once the chunks it reads have arrived, D2H per finished range); option no_pipeline is the plain
     H2D -> kernel -> D2H path.  Same bits."""
     import os
     lvl = d4est_b200.MeshLevel.brick((24, 20, 28), deg=3)   # 13 440 elements: above the pipeline threshold
     u = np.random.default_rng(3).uniform(-1, 1, lvl.local_nodes)
     a = lvl.apply_host(u)
-    os.environ["D4B_NO_PIPELINE"] = "1"
+    from d4est_b200 import capi
+    capi.check(capi.lib().d4b_set_option(b"no_pipeline", 1))
     try:
         b = lvl.apply_host(u)
     finally:
-        del os.environ["D4B_NO_PIPELINE"]
+        capi.check(capi.lib().d4b_set_option(b"no_pipeline", 0))
     assert np.array_equal(a, b) and np.isfinite(a).all() and np.abs(a).max() > 0
 
 
 def test_host_pipeline_late_pass_with_pinned_buffers():
     """With pinned (device-mapped) caller buffers the pipeline defers the elements that read a neighbour more than
-    one chunk ahead to a last launch that stores straight into the caller's Au (d4b_apply_host); D4B_NO_LATE_PASS=1
+    one chunk ahead to a last launch that stores straight into the caller's Au (d4b_apply_host); option no_late_pass
     makes every range wait for the last chunk it reads instead.  The deferred elements go through the kernel's
     three-round staging plan (a+ of their own record instead of -a- of the neighbour): equal to rounding."""
     import ctypes
@@ -90,13 +91,13 @@ def test_host_pipeline_late_pass_with_pinned_buffers():
             lvl.apply_host(hu, out=hAu)
             a = hAu.copy()
             assert np.isfinite(a).all()
-        os.environ["D4B_NO_LATE_PASS"] = "1"
+        capi.check(L.d4b_set_option(b"no_late_pass", 1))
         try:
             hAu[:] = np.nan
             lvl.apply_host(hu, out=hAu)
             b = hAu.copy()
         finally:
-            del os.environ["D4B_NO_LATE_PASS"]
+            capi.check(L.d4b_set_option(b"no_late_pass", 0))
         ref = lvl.apply_host(np.array(hu))       # pageable buffers: no late pass
         assert np.array_equal(b, ref)
         assert np.linalg.norm(a - ref) <= 1e-13 * np.linalg.norm(ref)

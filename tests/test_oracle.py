@@ -69,3 +69,87 @@ def test_solver_oracle_matches_reference_cg_eigs_and_cheby(golden_dir, name):
     u2, r2 = so.cheby_iterate(A, fx["sol_u_after_eigs"].copy(), rhs, 8, fx["sol_eig"][0] / 30., fx["sol_eig"][0])
     assert rel(u2, fx["sol_u_after_cheby"]) < 1e-11
     assert rel(r2, fx["sol_r_after_cheby"]) < 1e-10
+
+
+def test_product_1d_tables_match_the_reference_tables(golden_dir):
+    """d4est_b200/csrc/d4b_ops.c (closed forms) against the UNMODIFIED reference's own operator tables
+    (d4est_operators_fetch_* / apply_* on unit vectors, dumped by oracle/_ref/d4b_ops_dump into
+    tests/golden/ref_ops_tables.fix): GLL and Gauss rules, D, GLL->Gauss interpolation, p- and hp-prolongation."""
+    import ctypes
+    import d4est_b200
+    fx = fixture.load(os.path.join(golden_dir, "ref_ops_tables.fix"))
+    L = ctypes.CDLL(d4est_b200.LIB_PATH)
+    P = ctypes.c_void_p
+    for deg in range(1, 9):
+        N = deg + 1
+        D = np.zeros((N, N)); L.d4b_ops_diff(deg, D.ctypes.data_as(P))
+        assert np.abs(D.ravel() - fx[f"D{deg}"]).max() < 1e-13 * np.abs(D).max()
+        assert np.abs(dg_oracle.diff_matrix(deg).ravel() - fx[f"D{deg}"]).max() < 1e-12 * np.abs(D).max()
+        x = np.zeros(N); w = np.zeros(N)
+        L.d4b_ops_gll(deg, x.ctypes.data_as(P), w.ctypes.data_as(P))
+        assert np.abs(x - fx[f"gll_x{deg}"]).max() < 1e-15 and np.abs(w - fx[f"gll_w{deg}"]).max() < 1e-15
+        L.d4b_ops_gauss(N, x.ctypes.data_as(P), w.ctypes.data_as(P))
+        assert np.abs(x - fx[f"gauss_x{deg}"]).max() < 1e-15 and np.abs(w - fx[f"gauss_w{deg}"]).max() < 1e-15
+        for degq in range(deg, min(deg + 3, 10) + 1):
+            I = np.zeros((degq + 1, N)); L.d4b_ops_interp(deg, degq, 0, -1, I.ctypes.data_as(P))
+            assert np.abs(I.ravel() - fx[f"I{deg}_{degq}"]).max() < 1e-14
+            assert np.abs(dg_oracle.interp(deg, degq, 0).ravel() - fx[f"I{deg}_{degq}"]).max() < 1e-13
+        for degh in range(deg, 9):
+            Nh = degh + 1
+            Pm = np.zeros((Nh, N)); L.d4b_ops_prolong(deg, degh, -1, Pm.ctypes.data_as(P))
+            assert np.abs(Pm.ravel() - fx[f"P{deg}_{degh}"]).max() < 1e-14
+            for c in (0, 1):
+                L.d4b_ops_prolong(deg, degh, c, Pm.ctypes.data_as(P))
+                assert np.abs(Pm.ravel() - fx[f"HP{deg}_{degh}"].reshape(2, Nh * N)[c]).max() < 1e-14
+
+
+def _mg_fixture(ref_fixture_dir):
+    p = os.path.join(ref_fixture_dir, "mg_cubed_sphere_hp1.fix")
+    if not os.path.exists(p):
+        pytest.skip("multigrid fixture not built (needs /root/reference at build time)")
+    return fixture.load(p)
+
+
+def test_transfer_oracle_matches_reference_prolongation(ref_fixture_dir):
+    """solver_oracle.transfer over the hierarchy captured from the reference's own coarsening against the
+    reference's d4est_operators_apply_{p,hp}_prolong[_transpose] on probe vectors (hp case: 8 children of mixed
+    degree, p case: same cell, copies of families that 2:1 balance split again)."""
+    import solver_oracle as so
+    fx = _mg_fixture(ref_fixture_dir)
+    nl = int(fx["mg_meta"][0])
+    for l in range(nl - 1):
+        T = fixture.sub(fx, f"T{l}.")
+        r = so.transfer(T, T["probe_fine"], T["probe_coarse"].size, True)
+        assert np.linalg.norm(r - T["ref_restricted"]) < 1e-13 * np.linalg.norm(T["ref_restricted"])
+        p = so.transfer(T, T["probe_coarse"], T["probe_fine"].size, False)
+        assert np.linalg.norm(p - T["ref_prolonged"]) < 1e-13 * np.linalg.norm(T["ref_prolonged"])
+
+
+def test_krylov_oracles_match_reference_drivers(ref_fixture_dir):
+    """solver_oracle.fcg_solve / cg_solve against d4est_solver_fcg_solve / d4est_solver_cg_solve run by the
+    reference itself for exactly 25 iterations (no preconditioner) on the curved hp mesh."""
+    import solver_oracle as so
+    fx = _mg_fixture(ref_fixture_dir)
+    nl = int(fx["mg_meta"][0])
+    top = fixture.sub(fx, f"L{nl - 1}.")
+    A = lambda v: dg_oracle.apply(top, v)
+    rhs = fx["mg_rhs"]
+    u, k = so.fcg_solve(A, np.zeros(rhs.size), rhs, 25, 0., 1e-300)
+    assert np.linalg.norm(u - fx["krylov_fcg25_u"]) < 1e-9 * np.linalg.norm(fx["krylov_fcg25_u"])
+    u, k, _ = so.cg_solve(A, np.zeros(rhs.size), rhs, 25, 0., 1e-300)
+    assert k == 25 and np.linalg.norm(u - fx["krylov_cg25_u"]) < 1e-9 * np.linalg.norm(fx["krylov_cg25_u"])
+
+
+def test_vcycle_oracle_matches_reference_preconditioner(ref_fixture_dir):
+    """solver_oracle.mg_pc (V-cycle with Chebyshev smoother + cg_eigs + Chebyshev bottom solver on the captured
+    hierarchy) against the reference's own d4est_krylov_pc_multigrid_apply: first preconditioner application of
+    its MG-FCG solve."""
+    import solver_oracle as so
+    fx = _mg_fixture(ref_fixture_dir)
+    nl = int(fx["mg_meta"][0])
+    lv = [fixture.sub(fx, f"L{l}.") for l in range(nl)]
+    A = [(lambda v, t=t: dg_oracle.apply(t, v)) for t in lv]
+    tabs = [fixture.sub(fx, f"T{l}.") for l in range(nl - 1)]
+    sizes = [int(t["node_off"][int(t["hdr"][0])]) for t in lv]
+    z = so.mg_pc(A, tabs, sizes, fx["mg_r0"], so.mg_params(fx["mg_params"]))
+    assert np.linalg.norm(z - fx["mg_z0"]) < 1e-9 * np.linalg.norm(fx["mg_z0"])

@@ -56,10 +56,21 @@ def test_cg_and_fcg_match_oracle_iteration_counts(golden_dir):
     it, r2 = C.c_int(), C.c_double()
     check(lib().d4b_cg_solve(lvl.handle, U.ptr, R.ptr, 400, 0., 1e-10, C.byref(it), C.byref(r2), W.ptr, None))
     assert abs(it.value - io) <= 1 and rel(U.get(), uo) < 1e-7
-    uf, kf = so.fcg_solve(A, np.zeros(n), rhs, 400, 0., 1e-10)
+    # flexible CG, the arithmetic the reference performs (its direction update loses the old direction, see
+    # d4b_solver.cu): without a preconditioner it crawls, so compare a fixed 20 iterations state for state ...
+    uf, kf = so.fcg_solve(A, np.zeros(n), rhs, 20, 0., 1e-300)
     U2 = DevVec(n); res = C.c_double()
-    check(lib().d4b_fcg_solve(lvl.handle, U2.ptr, R.ptr, 400, 0., 1e-10, None, None, C.byref(it), C.byref(res), W.ptr, None))
-    assert abs(it.value - kf) <= 1 and rel(U2.get(), uf) < 1e-7
+    check(lib().d4b_fcg_solve(lvl.handle, U2.ptr, R.ptr, 20, 0., 1e-300, None, None, C.byref(it), C.byref(res), W.ptr, None))
+    assert it.value == 20 and rel(U2.get(), uf) < 1e-9
+    # ... and the textbook update (option) to convergence, iteration count +-1
+    uf, kf = so.fcg_solve(A, np.zeros(n), rhs, 400, 0., 1e-10, textbook=True)
+    check(lib().d4b_set_option(b"fcg_textbook_update", 1))
+    try:
+        U3 = DevVec(n)
+        check(lib().d4b_fcg_solve(lvl.handle, U3.ptr, R.ptr, 400, 0., 1e-10, None, None, C.byref(it), C.byref(res), W.ptr, None))
+    finally:
+        check(lib().d4b_set_option(b"fcg_textbook_update", 0))
+    assert abs(it.value - kf) <= 1 and rel(U3.get(), uf) < 1e-7
 
 
 def test_transfer_matches_oracle_and_is_adjoint():
@@ -84,8 +95,10 @@ def test_transfer_matches_oracle_and_is_adjoint():
 
 
 def test_mg_preconditioned_fcg_on_brick():
-    """BASELINE config 4 in miniature: MG (Chebyshev smoother + Chebyshev bottom solver) preconditioned
-    flexible CG to 1e-10; same iteration count (+-1) as the numpy restatement driving the same V-cycle."""
+    """BASELINE config 4 in miniature on a uniform brick hierarchy: MG (Chebyshev smoother + Chebyshev bottom
+    solver) preconditioned flexible CG reaches a true relative residual of 1e-9 in few iterations and beats
+    unpreconditioned CG by more than 2x.  (The +-1-iteration comparison with the REFERENCE's own solve is
+    tests/test_mg_reference_gpu.py, on the curved hp mesh and the hierarchy captured from d4est's coarsening.)"""
     deg, levels = 2, [d4est_b200.MeshLevel.brick(2, deg=2), d4est_b200.MeshLevel.brick(4, deg=2), d4est_b200.MeshLevel.brick(8, deg=2)]
     trs = [capi.Transfer(so.brick_transfer_table(2, deg)), capi.Transfer(so.brick_transfer_table(4, deg))]
     mg = capi.Multigrid(levels, trs, cheby_imax=8, cheby_eigs_cg_imax=10, bottom_imax=10, bottom_eigs_cg_imax=10)
@@ -97,8 +110,15 @@ def test_mg_preconditioned_fcg_on_brick():
     u = U.get()
     r = rhs - levels[-1].apply_host(u)
     assert np.linalg.norm(r) <= 1e-9 * np.linalg.norm(rhs)
-    assert it.value < 30
-    # unpreconditioned CG needs many more iterations on the same system
-    U2 = DevVec(n); it2 = C.c_int()
-    check(lib().d4b_fcg_solve(levels[-1].handle, U2.ptr, R.ptr, 2000, 0., 1e-10, None, None, C.byref(it2), C.byref(res), W.ptr, None))
-    assert it2.value > 2 * it.value
+    assert it.value < 100          # the reference's flexible-CG arithmetic (default)
+    check(lib().d4b_set_option(b"fcg_textbook_update", 1))
+    try:
+        Ut, itt = DevVec(n), C.c_int()
+        check(lib().d4b_mg_fcg_solve(mg.handle, Ut.ptr, R.ptr, 100, 0., 1e-10, C.byref(itt), C.byref(res), W.ptr, None))
+        assert itt.value < 30      # the textbook update: MG-preconditioned CG in a handful of iterations
+        # unpreconditioned CG needs many more iterations on the same system
+        U2 = DevVec(n); it2 = C.c_int()
+        check(lib().d4b_fcg_solve(levels[-1].handle, U2.ptr, R.ptr, 2000, 0., 1e-10, None, None, C.byref(it2), C.byref(res), W.ptr, None))
+        assert it2.value > 2 * itt.value
+    finally:
+        check(lib().d4b_set_option(b"fcg_textbook_update", 0))
