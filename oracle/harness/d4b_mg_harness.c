@@ -10,7 +10,7 @@
  *   4. with --gpu-check (needs a CUDA device): runs the same things through the d4est-facing entry points of the
  *      product glue IN THIS PROCESS, next to the reference, and prints the differences as one JSON line.
  *
- * usage: d4b_mg_harness <input> <amr: none|random_hp|uniform_h> <steps> <out.fix|-> [--gpu-check [ref_iterations]]
+ * usage: d4b_mg_harness <input> <amr: none|random_hp|uniform_h> <steps> <out.fix|-> [--gpu-check [ref_iterations] | --capture-only]
  *   With --gpu-check the minutes-long reference solve is not repeated: the reference side of the comparison is
  *   one reference V-cycle (z0 = PC(rhs), the first preconditioner application of the solve) and the reference
  *   operator applies, all run in this process; the reference iteration count comes from the fixture made by
@@ -78,6 +78,7 @@ int main(int argc, char **argv)
   if (argc < 5) { fprintf(stderr, "usage: see header of d4b_mg_harness.c\n"); return 2; }
   const char *input = argv[1], *amr = argv[2]; int steps = atoi(argv[3]); const char *out = argv[4];
   int gpu_check = argc > 5 && !strcmp(argv[5], "--gpu-check");
+  int capture_only = argc > 5 && !strcmp(argv[5], "--capture-only");   /* hierarchy + rhs only: no reference solve */
   int ref_iters_arg = argc > 6 ? atoi(argv[6]) : -1;
 
   sc_MPI_Comm comm = sc_MPI_COMM_WORLD;
@@ -123,7 +124,9 @@ int main(int argc, char **argv)
   d4est_elliptic_data_t vecs; memset(&vecs, 0, sizeof vecs);
   vecs.local_nodes = n; vecs.field_types = &ft; vecs.num_of_fields = 1;
   vecs.u = ustar; vecs.Au = rhs;
+  double t_apply = now_s();
   d4est_laplacian_with_opt_apply_aij(p4est, ghost, gd, &vecs, fl1, ops, geom, quad, factors, 0);
+  t_apply = now_s() - t_apply;
   vecs.u = u; vecs.Au = Au; vecs.rhs = rhs;
 
   d4est_solver_multigrid_t *mg = d4est_solver_multigrid_data_init(p4est, ops, geom, quad, &ghost, &gd, factors, ext, input);
@@ -136,7 +139,9 @@ int main(int argc, char **argv)
   d4est_krylov_pc_t pc_rec; pc_rec.pc_apply = rec_pc_apply; pc_rec.pc_setup = NULL; pc_rec.pc_data = &R; pc_rec.pc_ctx = NULL;
   double t0 = now_s(), t_ref = 0., res_ref = -1.;
   int it_ref = ref_iters_arg;
-  if (!gpu_check) {
+  if (capture_only) {
+    memcpy(R.r0, rhs, (size_t)n * 8); memset(R.z0, 0, (size_t)n * 8);
+  } else if (!gpu_check) {
     d4est_solver_fcg_solve(p4est, &vecs, &fcns, &ghost, &gd, ops, geom, quad, factors, &fp, &pc_rec, -1, -1);
     t_ref = now_s() - t0;
     /* iterations as d4b_fcg_solve counts them: the loop index at the break (fcg_improved.c:283) */
@@ -175,7 +180,7 @@ int main(int argc, char **argv)
     fix_write(f, "mg_res_hist", FIX_F64, R.count < MAXIT ? R.count : MAXIT, R.hist);
     fix_write(f, "mg_r0", FIX_F64, n, R.r0);
     fix_write(f, "mg_z0", FIX_F64, n, R.z0);
-    { /* the reference's Krylov drivers WITHOUT a preconditioner, a fixed 25 iterations from u = 0 on the same
+    if (!capture_only) { /* the reference's Krylov drivers WITHOUT a preconditioner, a fixed 25 iterations from u = 0 on the same
          system: pins the restated drivers (oracle/solver_oracle.py, d4b_fcg_solve, d4b_cg_solve) step by step */
       double *uk = P4EST_ALLOC_ZERO(double, n), *Ak = P4EST_ALLOC_ZERO(double, n);
       d4est_elliptic_data_t vk; d4est_elliptic_data_copy_ptrs(&vecs, &vk); vk.u = uk; vk.Au = Ak; vk.rhs = rhs;
@@ -228,9 +233,9 @@ int main(int argc, char **argv)
   }
   printf("{\"what\": \"reference_mg_fcg\", \"elements\": %d, \"nodes\": %d, \"levels\": %d, \"fcg_iterations\": %d, "
          "\"pc_applications\": %d, \"true_residual\": %.6e, \"rhs_norm\": %.6e, \"seconds_cpu\": %.3f, "
-         "\"err_vs_ustar\": %.3e",
-         (int)p4est->local_num_quadrants, n, nl, it_ref, R.count, res_ref, nrm2(rhs, n), t_ref, rel_l2(u, ustar, n));
-  for (int l = 0; l < nl; l++) printf(", \"L%d_elements\": %d", l, desc[l]->n_local);
+         "\"err_vs_ustar\": %.3e, \"seconds_reference_apply_top_level\": %.4f",
+         (int)p4est->local_num_quadrants, n, nl, it_ref, R.count, res_ref, nrm2(rhs, n), t_ref, rel_l2(u, ustar, n), t_apply);
+  for (int l = 0; l < nl; l++) printf(", \"L%d_elements\": %d, \"L%d_nodes\": %lld", l, desc[l]->n_local, l, (long long)desc[l]->node_off[desc[l]->n_local]);
   printf("}\n");
   fflush(stdout);
 
