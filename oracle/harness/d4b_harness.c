@@ -10,7 +10,7 @@
  *   4. optionally times the reference apply (bench.py cpu_baseline kind "reference").
  *
  * usage: d4b_harness <input> <amr: none|random_hp|uniform_h> <steps> <bc: zero|poly>
- *                    <u: polyrand|sinrand> <out.fix|-> [timing_reps]
+ *                    <u: polyrand|sinrand|poly> <out.fix|-> [timing_reps]
  */
 #include <pXest.h>
 #include <d4est_quadrature.h>
@@ -107,8 +107,10 @@ int main(int argc, char **argv)
   double *u = P4EST_ALLOC(double, n), *Au0 = P4EST_ALLOC_ZERO(double, n), *Au1 = P4EST_ALLOC_ZERO(double, n);
   d4est_mesh_init_field(p4est, u, !strcmp(ukind, "sinrand") ? sin_fcn : poly_fcn, ops, geom, factors,
                         INIT_FIELD_ON_LOBATTO, NULL);
-  srand(102321); /* Tests/Unit/d4est_test_laplacian_speedup.c:429-432 */
-  for (int i = 0; i < n; i++) u[i] += (double)rand() / (double)RAND_MAX;
+  if (strcmp(ukind, "poly") != 0) {   /* "poly": the pure polynomial of Tests/Unit/d4est_test_laplacian_consistency.c */
+    srand(102321); /* Tests/Unit/d4est_test_laplacian_speedup.c:429-432 */
+    for (int i = 0; i < n; i++) u[i] += (double)rand() / (double)RAND_MAX;
+  }
 
   d4est_elliptic_data_t vecs; memset(&vecs, 0, sizeof vecs);
   vecs.u = u; vecs.local_nodes = n; vecs.field_types = &ft; vecs.num_of_fields = 1;
@@ -155,7 +157,8 @@ int main(int argc, char **argv)
     fclose(f);
     d4est_b200_flatten_free(D);
   }
-  printf("{\"elements\": %d, \"nodes\": %d, \"Au_sum_baseline\": %.17g, \"Au_sum_with_opt\": %.17g, "
+  printf("{\"Au_baseline_33010\": %.17g, \"Au_with_opt_33010\": %.17g, ", n > 33010 ? Au0[33010] : 0., n > 33010 ? Au1[33010] : 0.);
+  printf("\"elements\": %d, \"nodes\": %d, \"Au_sum_baseline\": %.17g, \"Au_sum_with_opt\": %.17g, "
          "\"max_abs_diff_variants\": %.3e, \"t_baseline_s\": %.6f, \"t_with_opt_s\": %.6f, "
          "\"t_with_opt_best_s\": %.6f, \"reps\": %d}\n",
          (int)p4est->local_num_quadrants, n, s0, s1, maxdiff, t_base, t_opt, t_best, reps);

@@ -155,3 +155,17 @@ def test_back_to_back_device_applies_on_a_multi_bucket_mesh(golden_dir):
     for _ in range(60):
         lvl.apply_dev(U.ptr.value, V.ptr.value, 0)
     assert np.array_equal(V.get(), ref)
+
+
+def test_reference_golden_numbers_on_the_device(ref_fixture_dir):
+    """The golden numbers of the reference's own unit tests, from the CUDA path: Au sum 938.3617199677 on the level-1
+    mesh of d4est_test_laplacian_speedup, Au[33010] = -0.0034181705065613 of d4est_test_laplacian_consistency."""
+    p2, pw = os.path.join(ref_fixture_dir, "cubed_sphere_hp2.fix"), os.path.join(ref_fixture_dir, "wedge_consistency.fix")
+    if not (os.path.exists(p2) and os.path.exists(pw)):
+        pytest.skip("reference fixtures not built")
+    fx = fixture.load(p2)
+    Au = d4est_b200.MeshLevel(fx).apply_host(fx["u"])
+    assert abs(Au.sum() - 938.36171996774) < 1e-8
+    fw = fixture.load(pw)
+    Aw = d4est_b200.MeshLevel(fw).apply_host(fw["u"])
+    assert abs(Aw[33010] - (-0.0034181705065613010)) < 1e-12

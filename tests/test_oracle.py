@@ -153,3 +153,20 @@ def test_vcycle_oracle_matches_reference_preconditioner(ref_fixture_dir):
     sizes = [int(t["node_off"][int(t["hdr"][0])]) for t in lv]
     z = so.mg_pc(A, tabs, sizes, fx["mg_r0"], so.mg_params(fx["mg_params"]))
     assert np.linalg.norm(z - fx["mg_z0"]) < 1e-9 * np.linalg.norm(fx["mg_z0"])
+
+
+def test_reference_golden_numbers_are_reproduced_by_the_oracle_build(ref_fixture_dir):
+    """The numbers the reference's own unit tests print / assert, reproduced by oracle/_ref (the unmodified reference
+    compiled here): level-1 Au sum of d4est_test_laplacian_speedup (938.36171996774783 baseline, ...774669 with_opt,
+    SURVEY 8c) and Au[33010] = -0.0034181705065613 of d4est_test_laplacian_consistency.c:415-426."""
+    import json
+    p2 = os.path.join(ref_fixture_dir, "cubed_sphere_hp2.json")
+    pw = os.path.join(ref_fixture_dir, "wedge_consistency.json")
+    if not (os.path.exists(p2) and os.path.exists(pw)):
+        pytest.skip("reference fixtures not built")
+    j2 = json.load(open(p2)); jw = json.load(open(pw))
+    assert j2["elements"] == 1294 and j2["nodes"] == 35558
+    assert abs(j2["Au_sum_baseline"] - 938.36171996774783) < 1e-9 and abs(j2["Au_sum_with_opt"] - 938.36171996774669) < 1e-9
+    assert abs(jw["Au_baseline_33010"] - (-0.0034181705065613010)) < 1e-12     # the reference test itself allows 1e-3
+    fw = fixture.load(os.path.join(ref_fixture_dir, "wedge_consistency.fix"))
+    assert fw["Au_ref_baseline"][33010] == jw["Au_baseline_33010"]
