@@ -232,7 +232,7 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   if (!m) return;
   cudaFree(m->deg); cudaFree(m->node_off); cudaFree(m->degq); cudaFree(m->quad_off); cudaFree(m->G);
   cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost);
-  cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->host_work); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
+  cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->host_work); cudaFree(m->sc); cudaFree(m->dot_part); if (m->sc_h) cudaFreeHost(m->sc_h); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
   for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); cudaFree(m->fast[i].nrec); cudaFree(m->fast[i].v3_slots); }
   for (int i = 0; i < m->n_hp; i++) { cudaFree(m->hp[i].slots); cudaFree(m->hp[i].recs); }
   cudaFree(m->generic_list);

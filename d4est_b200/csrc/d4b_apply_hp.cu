@@ -48,8 +48,8 @@ __constant__ d4b_ops_dev c_hp_ops[2];
 template <int N, int Nq> struct hp_tab { double B[Nq * N], C[Nq * N], D[N * N]; };
 
 /* (N, Nq, spare) */
-#define HP_PAIRS(X) X(2, 2, 4) X(2, 3, 4) X(2, 4, 4) X(3, 3, 4) X(3, 4, 4) X(3, 5, 4) X(4, 4, 4) X(4, 5, 4) X(4, 6, 4) \
-                    X(5, 5, 2) X(5, 6, 2) X(5, 7, 2) X(6, 6, 2) X(6, 7, 2) X(6, 8, 2) X(7, 7, 1) X(7, 8, 1) X(7, 9, 1) \
+#define HP_PAIRS(X) X(2, 2, 4) X(2, 3, 4) X(2, 4, 4) X(2, 5, 4) X(3, 3, 4) X(3, 4, 4) X(3, 5, 4) X(3, 6, 4) X(4, 4, 4) X(4, 5, 4) X(4, 6, 4) X(4, 7, 4) \
+                    X(5, 5, 2) X(5, 6, 2) X(5, 7, 2) X(5, 8, 2) X(6, 6, 2) X(6, 7, 2) X(6, 8, 2) X(7, 7, 1) X(7, 8, 1) X(7, 9, 1) \
                     X(8, 8, 1) X(8, 9, 1) X(8, 10, 1)
 #define HP_MAXNP 8     /* neighbour N handled by the templated line tasks */
 #define HP_MAXNM 12

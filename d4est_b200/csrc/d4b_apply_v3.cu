@@ -40,7 +40,7 @@ struct v3_tab {
 };
 /* one immutable table per template instance: written once (per quadrature type), so launches of different
  * instances on different streams never race on it */
-#define V3_PAIRS(X) X(2, 2) X(2, 4) X(4, 4)
+#define V3_PAIRS(X) X(2, 2) X(2, 3) X(2, 4) X(3, 3) X(3, 4) X(4, 4)
 enum {
 #define X(a, b) V3I_##a##_##b,
   V3_PAIRS(X)

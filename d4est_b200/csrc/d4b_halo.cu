@@ -9,7 +9,6 @@
 
 static ncclComm_t g_comm = nullptr;
 static int g_rank = 0, g_nranks = 1;
-static double *g_red_dev = nullptr;
 
 #define D4B_NCCL(call)                                                                  \
   do { ncclResult_t r_ = (call);                                                        \
@@ -36,7 +35,6 @@ int d4b_comm_init(int rank, int nranks, const char *id128)
   ncclUniqueId id; memcpy(&id, id128, sizeof id);
   D4B_NCCL(ncclCommInitRank(&g_comm, nranks, id, rank));
   g_rank = rank; g_nranks = nranks;
-  D4B_CUDA(cudaMalloc((void **)&g_red_dev, 8 * sizeof(double)));
   return D4B_OK;
 }
 int d4b_comm_finalize(void)
@@ -67,12 +65,12 @@ int d4b_halo_exchange(d4b_mesh_t *m, const double *u_dev, void *stream)
 
 } /* extern C */
 
-int d4b_allreduce_sum_host(double *vals, int k, cudaStream_t st)
+/* sum over ranks of k device scalars, in place and in stream: the reductions of CG / FCG / cg_eigs / the V-cycle
+ * residual (sc_allreduce in the reference, e.g. Solver/d4est_solver_cg.c:139,165, fcg_improved.c:245) never leave
+ * the device */
+int d4b_allreduce_sum_dev(double *dev, int k, cudaStream_t st)
 {
   if (g_nranks == 1 || !g_comm) return D4B_OK;
-  D4B_CUDA(cudaMemcpyAsync(g_red_dev, vals, k * sizeof(double), cudaMemcpyHostToDevice, st));
-  D4B_NCCL(ncclAllReduce(g_red_dev, g_red_dev, (size_t)k, ncclDouble, ncclSum, g_comm, st));
-  D4B_CUDA(cudaMemcpyAsync(vals, g_red_dev, k * sizeof(double), cudaMemcpyDeviceToHost, st));
-  D4B_CUDA(cudaStreamSynchronize(st));
+  D4B_NCCL(ncclAllReduce(dev, dev, (size_t)k, ncclDouble, ncclSum, g_comm, st));
   return D4B_OK;
 }

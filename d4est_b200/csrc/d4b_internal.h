@@ -47,6 +47,7 @@ struct d4b_mesh {
   double *u_ghost;                 /* [ghost_nodes] received halo                        */
   int ghost_supplied;              /* d4b_set_ghost_host was called (single-process tests of the N > 1 layout) */
   double *u_stage, *Au_stage;      /* staging for d4b_apply_host                         */
+  double *sc, *dot_part, *sc_h;    /* device scalar block, reduction partials, pinned host mirror (d4b_solver.cu) */
   double *host_work;               /* 6 n doubles: staging + work of the host-vector solver entry points */
   int64_t bytes, alg_bytes;
   size_t generic_smem;
@@ -97,6 +98,14 @@ int d4b_v3_build_late(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges,
 int d4b_v3_range_need(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, const int *bounds, int *need_host, cudaStream_t st);
 /* split elements into fast buckets + generic list; D->hm == NULL means the uniform device-built brick */
 int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D);
+/* sync-free solver pieces (d4b_solver.cu) used by the multigrid */
+int d4b_cg_eigs_dev(d4b_mesh *m, double *u, const double *rhs, int imax, int use_new, double *work_3n, cudaStream_t st);
+int d4b_cheby_dev(d4b_mesh *m, double *u, const double *rhs, double *r, int iter, const double *eig_src, double mult,
+                  double *eig_dst, double ratio, double *work_2n, cudaStream_t st);
+double *d4b_scalar_tmax(d4b_mesh *m);
+int d4b_norm2_dev(d4b_mesh *m, const double *r, cudaStream_t st);
+int d4b_read_r2(d4b_mesh *m, double *r2, cudaStream_t st);
+int d4b_allreduce_sum_dev(double *dev, int k, cudaStream_t st);
 int d4b_mesh_make_streams(d4b_mesh *m);
 
 #define D4B_CUDA(call)                                                                   \

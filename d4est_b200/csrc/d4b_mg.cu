@@ -112,7 +112,7 @@ struct d4b_mg {
   d4b_mesh **lvl;            /* 0 = coarsest ... n_levels-1 = finest */
   d4b_mg_transfer **tr;      /* tr[l]: between level l (coarse) and l+1 (fine) */
   d4b_mg_params_t par;
-  double *eigs;              /* per level spectral bound (cheby->eigs[level]) */
+  double *eigs;              /* DEVICE: per level spectral bound (cheby->eigs[level]) */
   double *u, *rhs, *r;       /* per-level stacked work vectors for levels < finest */
   int64_t *off;              /* offset of level l inside the stacks */
   double *work;              /* 3 * max nodes */
@@ -175,7 +175,7 @@ int d4b_mg_create(int n_levels, d4b_mesh_t **levels, d4b_mg_transfer_t **transfe
   d4b_mg *g = (d4b_mg *)calloc(1, sizeof *g);
   g->n_levels = n_levels; g->par = *par;
   g->lvl = (d4b_mesh **)malloc(n_levels * sizeof(void *)); g->tr = (d4b_mg_transfer **)malloc(n_levels * sizeof(void *));
-  g->off = (int64_t *)calloc(n_levels + 1, sizeof(int64_t)); g->eigs = (double *)calloc(n_levels, sizeof(double));
+  g->off = (int64_t *)calloc(n_levels + 1, sizeof(int64_t)); D4B_CUDA(cudaMalloc((void **)&g->eigs, n_levels * sizeof(double))); D4B_CUDA(cudaMemset(g->eigs, 0, n_levels * sizeof(double)));
   int64_t tot = 0, mx = 0;
   for (int l = 0; l < n_levels; l++) {
     g->lvl[l] = levels[l]; g->tr[l] = l < n_levels - 1 ? transfers[l] : nullptr;
@@ -193,9 +193,10 @@ void d4b_mg_destroy(d4b_mg_t *g)
 {
   if (!g) return;
   cudaFree(g->u); cudaFree(g->rhs); cudaFree(g->r); cudaFree(g->work); cudaFree(g->hbuf);
-  free(g->lvl); free(g->tr); free(g->off); free(g->eigs); free(g);
+  free(g->lvl); free(g->tr); free(g->off); cudaFree(g->eigs); free(g);
 }
-int d4b_mg_get_eigs(d4b_mg_t *g, double *eigs) { memcpy(eigs, g->eigs, g->n_levels * sizeof(double)); return D4B_OK; }
+int d4b_mg_get_eigs(d4b_mg_t *g, double *eigs)
+{ D4B_CUDA(cudaMemcpy(eigs, g->eigs, g->n_levels * sizeof(double), cudaMemcpyDeviceToHost)); return D4B_OK; }
 
 } /* extern C */
 
@@ -207,12 +208,15 @@ static int mg_smooth(d4b_mg *g, int l, double *u, const double *rhs, double *r, 
   int compute = down ? !(p.eigs_reuse_fromlastvcycle && g->vcycles_done != 0)
                      : !(p.eigs_reuse_fromdownvcycle || (p.eigs_reuse_fromlastvcycle && g->vcycles_done != 0));
   int rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  /* nothing comes back to the host: the bound goes from the level's scalar block to g->eigs[l] (device) inside the
+   * coefficient kernel of the Chebyshev sweep */
   if (compute) {
-    if ((rc = d4b_cg_eigs(g->lvl[l], u, rhs, p.cheby_eigs_cg_imax, p.use_new_cg_eigs, &g->eigs[l], g->work, stream))) return rc;
-    g->eigs[l] *= p.cheby_eigs_max_multiplier;
+    if ((rc = d4b_cg_eigs_dev(g->lvl[l], u, rhs, p.cheby_eigs_cg_imax, p.use_new_cg_eigs, g->work, st))) return rc;
+    return d4b_cheby_dev(g->lvl[l], u, rhs, r, p.cheby_imax, d4b_scalar_tmax(g->lvl[l]), p.cheby_eigs_max_multiplier,
+                         g->eigs + l, p.cheby_eigs_lmax_lmin_ratio, g->work, st);
   }
-  return d4b_cheby_iterate(g->lvl[l], u, rhs, r, p.cheby_imax, g->eigs[l] / p.cheby_eigs_lmax_lmin_ratio, g->eigs[l], 1,
-                           g->work, stream);
+  return d4b_cheby_dev(g->lvl[l], u, rhs, r, p.cheby_imax, g->eigs + l, 1.0, g->eigs + l, p.cheby_eigs_lmax_lmin_ratio, g->work, st);
 }
 
 extern "C" {
@@ -243,10 +247,9 @@ int d4b_mg_vcycle(d4b_mg_t *g, double *u, const double *rhs, double *r2_local, v
     if (p.bottom_kind == 1) { /* mg_bottom_solver_cg (bottom_solver_cg.c:59-190) */
       if ((rc = d4b_cg_solve(m0, u0, f0, p.bottom_imax, p.bottom_atol, p.bottom_rtol, nullptr, nullptr, g->work, stream))) return rc;
     } else {                  /* mg_bottom_solver_cheby (bottom_solver_cheby.c:59-113) */
-      double eig = 0.;
-      if ((rc = d4b_cg_eigs(m0, u0, f0, p.bottom_eigs_cg_imax, p.use_new_cg_eigs, &eig, g->work, stream))) return rc;
-      eig *= p.bottom_eigs_max_multiplier; g->eigs[0] = eig;
-      if ((rc = d4b_cheby_iterate(m0, u0, f0, r0, p.bottom_imax, eig / p.bottom_eigs_lmax_lmin_ratio, eig, 1, g->work, stream))) return rc;
+      if ((rc = d4b_cg_eigs_dev(m0, u0, f0, p.bottom_eigs_cg_imax, p.use_new_cg_eigs, g->work, st))) return rc;
+      if ((rc = d4b_cheby_dev(m0, u0, f0, r0, p.bottom_imax, d4b_scalar_tmax(m0), p.bottom_eigs_max_multiplier, g->eigs,
+                              p.bottom_eigs_lmax_lmin_ratio, g->work, st))) return rc;
     }
   }
   /* up sweep (:1168-1300): prolong the correction, add, post-smooth */
@@ -258,7 +261,10 @@ int d4b_mg_vcycle(d4b_mg_t *g, double *u, const double *rhs, double *r2_local, v
     if ((rc = d4b_vec_axpy(g->lvl[l + 1]->local_nodes, 1.0, rf, uf, stream))) return rc;
     if ((rc = mg_smooth(g, l + 1, uf, ff, rf, 0, stream))) return rc;
   }
-  if (r2_local) return d4b_vec_dot(g->lvl[top]->local_nodes, rtop, rtop, r2_local, stream);
+  if (r2_local) {   /* the only host read of a V-cycle, and only when the caller wants the residual */
+    if ((rc = d4b_norm2_dev(g->lvl[top], rtop, st))) return rc;
+    return d4b_read_r2(g->lvl[top], r2_local, st);
+  }
   return D4B_OK;
 }
 
@@ -292,6 +298,16 @@ int d4b_mg_pc_apply(void *ctx, const double *r_dev, double *z_dev, void *stream)
 {
   d4b_mg *g = (d4b_mg *)ctx;
   D4B_CUDA(cudaMemsetAsync(z_dev, 0, g->lvl[g->n_levels - 1]->local_nodes * sizeof(double), (cudaStream_t)stream));
+  if (g->par.vcycle_imax == 1 && g->par.vcycle_rtol < 1. && g->par.vcycle_atol == 0.) {
+    /* d4est_solver_multigrid_solve from a zero guess with vcycle_imax = 1: the initial residual is r itself, the
+     * loop test r2 > rtol^2 r2 + atol^2 holds for every nonzero r, so exactly one V-cycle runs (multigrid.c:1463);
+     * neither the initial residual nor the final one is needed: nothing is read back, the whole application
+     * enqueues without a host synchronisation */
+    g->vcycles_done = 0;
+    int rc = d4b_mg_vcycle(g, z_dev, r_dev, nullptr, stream);
+    g->vcycles_done = 1;
+    return rc;
+  }
   return d4b_mg_solve(g, z_dev, r_dev, nullptr, nullptr, stream);
 }
 

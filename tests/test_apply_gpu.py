@@ -119,7 +119,8 @@ def test_register_blocked_kernel_equals_line_kernel_and_generic(name, ref_fixtur
     assert rel(out["v3"], out["v3_three_rounds"]) < 1e-13
 
 
-@pytest.mark.parametrize("dims,deg", [((5, 3, 7), 3), ((9, 9, 9), 3), ((17, 4, 3), 1), ((6, 10, 2), 1), ((2, 2, 2), 3)])
+@pytest.mark.parametrize("dims,deg", [((5, 3, 7), 3), ((9, 9, 9), 3), ((17, 4, 3), 1), ((6, 10, 2), 1), ((2, 2, 2), 3),
+                                      ((7, 5, 3), 2), ((8, 8, 8), 2)])
 def test_register_blocked_kernel_on_odd_bricks(dims, deg):
     """Bricks whose element count is not a multiple of the warp batch and whose Morton families are incomplete
     (odd extents): the shuffle exchange / one-round staging plan, the three-round plan and the line-task kernel
