@@ -441,7 +441,7 @@ int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D)
       if (D->hm_begin[e + 1] - D->hm_begin[e] != 6) ok = false;
       for (int r = D->hm_begin[e]; ok && r < D->hm_begin[e + 1]; r++) {
         const d4b_hm_t &h = D->hm[r];
-        if (h.child_m >= 0 || h.child_p >= 0 || h.degq != dq || rec[h.f_m] >= 0) { ok = false; break; }
+        if (h.child_m >= 0 || h.child_p >= 0 || h.degq != dq || rec[h.f_m] >= 0 || (h.nbr < 0 && h.pad == 1)) { ok = false; break; }
         if (h.nbr >= 0 && D->deg[h.nbr] != dg) { ok = false; break; }
         rec[h.f_m] = r;
       }

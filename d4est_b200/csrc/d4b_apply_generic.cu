@@ -204,6 +204,10 @@ d4b_apply_generic_kernel(const d4b_gen_args A)
       } else {
         double g = (h.g_off >= 0) ? A.bc_g[h.g_off + q] : 0.;
         jump = um - g; t1v = -qm; sjs = F[3 * Nm2 + q]; hs = -1.0;
+        if (h.pad == 1) { /* Robin: sj (alpha u - beta), fac row 3 = sj alpha, bc_g = sj beta, rows 0-2 zero */
+          FH[q] = w * (sjs * um - g); FH[Nm2 + q] = 0.; FH[2 * Nm2 + q] = 0.; FH[3 * Nm2 + q] = 0.;
+          continue;
+        }
       }
       FH[q] = w * (t1v + sjs * jump);
       FH[Nm2 + q] = w * hs * am0 * jump;

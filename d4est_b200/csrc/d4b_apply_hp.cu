@@ -38,7 +38,7 @@ struct hp_rec {       /* 32 bytes: one half-mortar, resolved once per level */
   int64_t fac_off;    /* my factor block: a-[3], (a+[3],) sj*sigma, Nm^2 each                           */
   int64_t g_off;      /* boundary: Dirichlet data or -1                                                */
   int64_t nbr_u;      /* >= 0 offset into u; < 0: -(offset into u_ghost) - 1                           */
-  int32_t code;       /* bits 0-2 f_m, 3-5 f_p, 6-8 tcode, 9-11 child_m+1, 12-14 child_p+1, 15 boundary */
+  int32_t code;       /* bits 0-2 f_m, 3-5 f_p, 6-8 tcode, 9-11 child_m+1, 12-14 child_p+1, 15 boundary, 16 Robin */
   int32_t dims;       /* Nm | Np << 8                                                                  */
 };
 struct hp_slot { int64_t node_off, quad_off; int32_t rec_begin, nrec; int64_t pad; };
@@ -374,6 +374,10 @@ __global__ void __launch_bounds__(128, (N <= 4 ? 4 : (Nq <= 6 ? 3 : 2))) d4b_app
         } else {
           const double gv = R.g_off >= 0 ? __ldg(A.bc_g + R.g_off + q) : 0.;
           jump = um - gv; t1 = -qm; sjs = __ldg(F + 3 * Nm2 + q); hs = -1.0;
+          if ((R.code >> 16) & 1) { /* Robin: sj (alpha u - beta); rows 0-2 of the block are zero */
+            RB[q] = w * (sjs * um - gv); RB[Nm2 + q] = 0.; RB[2 * Nm2 + q] = 0.; RB[3 * Nm2 + q] = 0.;
+            continue;
+          }
         }
         const double wj = w * hs * jump;
         RB[q] = w * (t1 + sjs * jump);
@@ -505,7 +509,7 @@ int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_
         R.nbr_u = h.nbr < nl ? D->node_off[h.nbr] : -(D->node_off[h.nbr] - D->node_off[nl]) - 1;
       }
       R.code = (h.f_m & 7) | (((bnd ? 0 : h.f_p) & 7) << 3) | ((h.tcode & 7) << 6) | ((h.child_m + 1) << 9) |
-               (((bnd ? -1 : h.child_p) + 1) << 12) | (bnd << 15);
+               (((bnd ? -1 : h.child_p) + 1) << 12) | (bnd << 15) | ((bnd && h.pad == 1) << 16);
       R.dims = (h.degq + 1) | (Np << 8);
       b.recs.push_back(R);
     }

@@ -30,6 +30,7 @@ typedef struct {
    * d4est_laplacian_with_opt_flux_data_t or from the baseline twin's d4est_laplacian_flux_data_t */
   d4est_laplacian_with_opt_flux_sipg_params_t *sp;   /* common leading fields of both sipg parameter structs */
   d4est_laplacian_bc_t bc_type; void *bc_data;
+  int baseline;     /* flux data of the baseline twin: its Robin callbacks take ITS boundary-data struct */
   int n_local;
   rec_t *rec; size_t nrec, caprec;
   double *fac; size_t nfac, capfac;
@@ -189,6 +190,50 @@ static void record_interface(p4est_t *p4est, d4est_element_data_t **e_m, int fac
   (void)geom; (void)quad;
 }
 
+/* Robin boundary face: Au += Lift(E^T w sj (alpha u - beta)), no gradient terms
+ * (d4est_laplacian_with_opt_flux_sipg_robin_aux, dGMath/d4est_laplacian_with_opt_flux_sipg.c:377-476; twin
+ * d4est_laplacian_flux_sipg_robin_aux).  alpha = robin_coeff and beta = robin_rhs are host callbacks of the mortar
+ * point coordinates; they are evaluated ONCE here.  The callbacks also receive the reference's boundary-data struct:
+ * it is handed over with its geometric members filled (coordinates, normals, sj, h, metric) and the members that
+ * depend on u left NULL -- a coefficient that reads u would make the operator nonlinear and cannot be tabulated. */
+static void record_boundary_robin(recorder_t *R, d4est_element_data_t *e_m, int f_m, int mortar_side_id_m,
+                                  d4est_mesh_data_t *factors)
+{
+  d4est_laplacian_with_opt_robin_bc_t *bc = (d4est_laplacian_with_opt_robin_bc_t *)R->bc_data;
+  int degq = e_m->deg_quad, nq = degq + 1, n2 = nq * nq;
+  size_t s0 = (size_t)factors->local_strides[e_m->id].mortar_quad_stride[f_m];
+  size_t b0 = (size_t)3 * factors->local_strides[e_m->id].boundary_quad_stride[f_m];
+  double *sj = &factors->sj_m_mortar_quad[s0];
+  d4est_laplacian_with_opt_flux_boundary_data_t bd; memset(&bd, 0, sizeof bd);
+  d4est_quadrature_mortar_t fo;
+  fo.dq = e_m->dq; fo.tree = e_m->tree; fo.face = f_m; fo.mortar_side_id = mortar_side_id_m;
+  fo.mortar_subface_id = 0; fo.q[0] = e_m->q[0]; fo.q[1] = e_m->q[1]; fo.q[2] = e_m->q[2];
+  bd.face_object = &fo; bd.deg_mortar_quad = degq; bd.face_nodes_m_quad = n2;
+  bd.face_nodes_m_lobatto = d4est_lgl_get_nodes(2, e_m->deg);
+  bd.sj_on_f_m_quad = sj; bd.h_quad = &factors->hm_mortar_quad[s0];
+  for (int d = 0; d < 3; d++) {
+    bd.n_on_f_m_quad[d] = &factors->n_m_mortar_quad[3 * s0 + (size_t)d * n2];
+    bd.xyz_on_f_m_quad[d] = &factors->xyz_m_mortar_quad[b0 + (size_t)d * n2];
+    bd.xyz_on_f_m_lobatto[d] = &factors->xyz_m_mortar_lobatto[b0 + (size_t)d * n2];
+    for (int d2 = 0; d2 < 3; d2++) bd.drst_dxyz_quad[d][d2] = &factors->drst_dxyz_m_mortar_quad[9 * s0 + (size_t)(d + 3 * d2) * n2];
+  }
+  rec_t r; memset(&r, 0, sizeof r);
+  r.elem = e_m->id;
+  r.hm.nbr = -1; r.hm.f_m = (int8_t)f_m; r.hm.f_p = -1; r.hm.tcode = 1; r.hm.pad = 1;
+  r.hm.child_m = -1; r.hm.child_p = -1; r.hm.degq = (int8_t)degq; r.hm.face_slot = (int8_t)f_m;
+  r.hm.fac_off = (int64_t)R->nfac; r.hm.g_off = (int64_t)R->ng; r.nfac = 4 * n2;
+  double *F = grow(&R->fac, &R->nfac, &R->capfac, (size_t)4 * n2);
+  double *g = grow(&R->g, &R->ng, &R->capg, (size_t)n2);
+  for (int k = 0; k < n2; k++) {
+    double x = bd.xyz_on_f_m_quad[0][k], y = bd.xyz_on_f_m_quad[1][k], z = bd.xyz_on_f_m_quad[2][k];
+    F[k] = F[n2 + k] = F[2 * n2 + k] = 0.;
+    /* the twin's callbacks expect d4est_laplacian_flux_boundary_data_t, a different layout: they get NULL */
+    F[3 * n2 + k] = sj[k] * bc->robin_coeff(x, y, z, bc->user, R->baseline ? NULL : &bd, k);
+    g[k] = sj[k] * bc->robin_rhs(x, y, z, bc->user, R->baseline ? NULL : &bd, k);
+  }
+  push_rec(R, &r);
+}
+
 /* Recording twin of d4est_laplacian_with_opt_flux_boundary (…_with_opt_flux.c:25) +
  * d4est_laplacian_with_opt_flux_sipg_dirichlet_aux (…_flux_sipg.c:15-191). */
 static void record_boundary(p4est_t *p4est, d4est_element_data_t *e_m, int f_m,
@@ -197,8 +242,9 @@ static void record_boundary(p4est_t *p4est, d4est_element_data_t *e_m, int f_m,
                             d4est_mesh_data_t *factors, void *ctx)
 {
   recorder_t *R = (recorder_t *)ctx;
+  if (R->bc_type == BC_ROBIN) { record_boundary_robin(R, e_m, f_m, mortar_side_id_m, factors); return; }
   if (R->bc_type != BC_DIRICHLET)
-    D4EST_ABORT("d4est_b200: only BC_DIRICHLET is implemented on the device path");
+    D4EST_ABORT("d4est_b200: boundary condition type not implemented on the device path");
   d4est_laplacian_with_opt_dirichlet_bc_t *bc = (d4est_laplacian_with_opt_dirichlet_bc_t *)R->bc_data;
   int degq = e_m->deg_quad, nq = degq + 1, n2 = nq * nq;
   int nl2 = d4est_lgl_get_nodes(2, e_m->deg);
@@ -247,7 +293,7 @@ static void record_boundary(p4est_t *p4est, d4est_element_data_t *e_m, int f_m,
 
 /* -------------------------------------------------------------------- flatten */
 static d4b_mesh_desc_t *flatten_impl(p4est_t *p4est, d4est_ghost_t *ghost, void *sipg_params,
-                                     d4est_laplacian_bc_t bc_type, void *bc_data, d4est_operators_t *ops,
+                                     d4est_laplacian_bc_t bc_type, void *bc_data, int baseline, d4est_operators_t *ops,
                                      d4est_geometry_t *geom, d4est_quadrature_t *quad, d4est_mesh_data_t *factors);
 
 d4b_mesh_desc_t *d4est_b200_flatten(p4est_t *p4est, d4est_ghost_t *ghost,
@@ -256,7 +302,7 @@ d4b_mesh_desc_t *d4est_b200_flatten(p4est_t *p4est, d4est_ghost_t *ghost,
                                     d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
 {
   if (flux_data->flux_type != FLUX_SIPG) D4EST_ABORT("d4est_b200: only the SIPG flux is implemented");
-  return flatten_impl(p4est, ghost, flux_data->flux_data, flux_data->bc_type, flux_data->bc_data, ops, geom, quad, factors);
+  return flatten_impl(p4est, ghost, flux_data->flux_data, flux_data->bc_type, flux_data->bc_data, 0, ops, geom, quad, factors);
 }
 
 /* Same tables from the baseline twin's flux data (d4est_laplacian_flux_data_t, dGMath/d4est_laplacian_flux.h):
@@ -269,11 +315,11 @@ d4b_mesh_desc_t *d4est_b200_flatten_baseline(p4est_t *p4est, d4est_ghost_t *ghos
                                              d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
 {
   if (fd->flux_type != FLUX_SIPG) D4EST_ABORT("d4est_b200: only the SIPG flux is implemented");
-  return flatten_impl(p4est, ghost, fd->flux_data, fd->bc_type, fd->bc_data, ops, geom, quad, factors);
+  return flatten_impl(p4est, ghost, fd->flux_data, fd->bc_type, fd->bc_data, 1, ops, geom, quad, factors);
 }
 
 static d4b_mesh_desc_t *flatten_impl(p4est_t *p4est, d4est_ghost_t *ghost, void *sipg_params,
-                                     d4est_laplacian_bc_t bc_type, void *bc_data, d4est_operators_t *ops,
+                                     d4est_laplacian_bc_t bc_type, void *bc_data, int baseline, d4est_operators_t *ops,
                                      d4est_geometry_t *geom, d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
 {
   int nl = (int)p4est->local_num_quadrants;
@@ -335,7 +381,7 @@ static d4b_mesh_desc_t *flatten_impl(p4est_t *p4est, d4est_ghost_t *ghost, void 
   /* faces: one walk of the reference iterator with recording callbacks */
   recorder_t R; memset(&R, 0, sizeof R);
   R.p4est = p4est; R.ghost = ghost; R.n_local = nl; R.quad_type = D->quad_type;
-  R.sp = (d4est_laplacian_with_opt_flux_sipg_params_t *)sipg_params; R.bc_type = bc_type; R.bc_data = bc_data;
+  R.sp = (d4est_laplacian_with_opt_flux_sipg_params_t *)sipg_params; R.bc_type = bc_type; R.bc_data = bc_data; R.baseline = baseline;
   d4est_mortars_with_opt_fcn_ptrs_t fp;
   fp.flux_interface_fcn = record_interface; fp.flux_boundary_fcn = record_boundary; fp.user_ctx = &R;
   d4est_mortars_with_opt_compute_flux_on_local_elements(p4est, ghost, ops, geom, quad, factors, &fp);

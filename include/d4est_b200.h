@@ -54,7 +54,8 @@ typedef struct d4b_hm {
   int8_t degq;      /* mortar quadrature degree = max(deg_quad_m, deg_quad_p)
                        (dGMath/d4est_laplacian_with_opt_flux.c:302-316)                 */
   int8_t face_slot; /* 0..5 = f_m (kept for alignment / debugging)                      */
-  int8_t pad;
+  int8_t pad;       /* boundary records: 0 = Dirichlet, 1 = Robin (fac rows 0-2 zero, row 3 = sj*alpha,
+                       bc_g = sj*beta at the mortar points; ..._flux_sipg.c:377-476)                  */
   int32_t pad0;     /* explicit: keeps the 8-byte fields aligned, sizeof == 40        */
   int64_t fac_off;  /* offset in doubles into fac[]: [7][Nqm^2] = a_m[3], a_p[3], sj*sigma
                        (interior) or [4][Nqm^2] = a_m[3], sj*sigma (boundary)            */

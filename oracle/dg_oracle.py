@@ -182,7 +182,10 @@ def apply(fx, u, u_ghost=None):
                 gb = bcg[h["g_off"]:h["g_off"] + n2] if h["g_off"] >= 0 else 0.0
                 jump = mq[0] - gb
                 t1 = -qm; hs = -1.0                       # sipg.c:139-191 (Dirichlet)
-            FH = np.stack([w2 * (t1 + sjs * jump)] + [w2 * hs * am[l] * jump for l in range(3)])
+            if h["nbr"] < 0 and h["pad"] == 1:            # Robin, sipg.c:377-476: sj (alpha u - beta), no gradient terms
+                FH = np.stack([w2 * (sjs * mq[0] - gb)] + [np.zeros(n2)] * 3)
+            else:
+                FH = np.stack([w2 * (t1 + sjs * jump)] + [w2 * hs * am[l] * jump for l in range(3)])
             back = np.einsum("qa,pb,cpq->cba", Ea, Eb, FH.reshape(4, Nm, Nm)).reshape(4, N * N)
             fi = face_index(N, int(h["f_m"]))
             acc[fi] += back[0]

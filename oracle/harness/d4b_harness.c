@@ -9,7 +9,7 @@
  *      flat tables + u + reference Au to a fixture file (format: oracle/fixture.py),
  *   4. optionally times the reference apply (bench.py cpu_baseline kind "reference").
  *
- * usage: d4b_harness <input> <amr: none|random_hp|uniform_h> <steps> <bc: zero|poly>
+ * usage: d4b_harness <input> <amr: none|random_hp|uniform_h> <steps> <bc: zero|poly|robin>
  *                    <u: polyrand|sinrand|poly> <out.fix|-> [timing_reps]
  */
 #include <pXest.h>
@@ -33,6 +33,17 @@
 static double poly_fcn(double x, double y, double z, void *user) { (void)user; return x * x + y * y + z * z; }
 static double sin_fcn(double x, double y, double z, void *user)
 { (void)user; return sin(M_PI * x) * sin(M_PI * y) * sin(M_PI * z); }
+
+/* Robin data alpha u + du/dn-type condition: sj (alpha u - beta), alpha(x) as in the reference's Lorentzian problem
+ * (Problems/Poisson/poisson_lorentzian_fcns.h:22-37), beta(x) nonzero so that the right-hand-side part is exercised */
+static double robin_coeff_opt(double x, double y, double z, void *user, d4est_laplacian_with_opt_flux_boundary_data_t *bd, int i)
+{ (void)user; (void)bd; (void)i; double r2 = x * x + y * y + z * z; return sqrt(r2) / (1. + r2); }
+static double robin_rhs_opt(double x, double y, double z, void *user, d4est_laplacian_with_opt_flux_boundary_data_t *bd, int i)
+{ (void)user; (void)bd; (void)i; return 0.3 + 0.1 * x - 0.2 * y * z; }
+static double robin_coeff_base(double x, double y, double z, void *user, d4est_laplacian_flux_boundary_data_t *bd, int i)
+{ return robin_coeff_opt(x, y, z, user, NULL, i); }
+static double robin_rhs_base(double x, double y, double z, void *user, d4est_laplacian_flux_boundary_data_t *bd, int i)
+{ return robin_rhs_opt(x, y, z, user, NULL, i); }
 
 static void ref_apply_lhs(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost_data_t *gd, d4est_elliptic_data_t *v,
                           d4est_operators_t *ops, d4est_geometry_t *geom, d4est_quadrature_t *quad,
@@ -101,8 +112,13 @@ int main(int argc, char **argv)
   bcd.dirichlet_fcn = !strcmp(bc, "zero") ? zero_fcn : poly_fcn;
   bcd.eval_method = EVAL_BNDRY_FCN_ON_LOBATTO;
   bcd.user = NULL;
-  d4est_laplacian_flux_data_t *fl0 = d4est_laplacian_flux_new(p4est, input, BC_DIRICHLET, &bcd);
-  d4est_laplacian_with_opt_flux_data_t *fl1 = d4est_laplacian_with_opt_flux_new(p4est, input, BC_DIRICHLET, &bcd);
+  d4est_laplacian_robin_bc_t rb0; rb0.robin_coeff = robin_coeff_base; rb0.robin_rhs = robin_rhs_base; rb0.user = NULL;
+  d4est_laplacian_with_opt_robin_bc_t rb1; rb1.robin_coeff = robin_coeff_opt; rb1.robin_rhs = robin_rhs_opt; rb1.user = NULL;
+  const int robin = !strcmp(bc, "robin");
+  d4est_laplacian_flux_data_t *fl0 = robin ? d4est_laplacian_flux_new(p4est, input, BC_ROBIN, &rb0)
+                                           : d4est_laplacian_flux_new(p4est, input, BC_DIRICHLET, &bcd);
+  d4est_laplacian_with_opt_flux_data_t *fl1 = robin ? d4est_laplacian_with_opt_flux_new(p4est, input, BC_ROBIN, &rb1)
+                                                    : d4est_laplacian_with_opt_flux_new(p4est, input, BC_DIRICHLET, &bcd);
 
   double *u = P4EST_ALLOC(double, n), *Au0 = P4EST_ALLOC_ZERO(double, n), *Au1 = P4EST_ALLOC_ZERO(double, n);
   d4est_mesh_init_field(p4est, u, !strcmp(ukind, "sinrand") ? sin_fcn : poly_fcn, ops, geom, factors,
