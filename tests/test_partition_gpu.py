@@ -51,6 +51,22 @@ def test_nccl_world_size_2(golden_dir):
            os.path.join(golden_dir, "cubed_sphere_hp1.fix"), "gpu"]
     r = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
+    print(r.stdout[-1500:])
+
+
+def test_nccl_world_size_2_krylov_reductions(golden_dir):
+    """Two ranks, two GPUs: CG and flexible CG on the partitioned brick (halo over ncclSend/Recv inside every apply,
+    dots over ncclAllReduce on device scalars) reproduce the 1-rank iterates and the 1-rank iteration count."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29521", os.path.join(ROOT, "tests", "mp_halo_worker.py"),
+           os.path.join(golden_dir, "brick_p3_l2.fix"), "gpu", "krylov"]
+    r = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:]
+    print(r.stdout[-1500:])
 
 
 def _morton_order(nx, ny, nz):
