@@ -130,7 +130,7 @@ __device__ __forceinline__ int hp_tcode_src(int tcode, int n, int a, int b)
 }
 
 template <int N, int Nq>
-__global__ void __launch_bounds__(128, (N <= 4 ? 4 : (Nq <= 6 ? 3 : 2))) d4b_apply_hp_kernel(const hp_args A)
+__global__ void __launch_bounds__(128, 4) d4b_apply_hp_kernel(const hp_args A)
 {
   using L = HL<N, Nq>;
   constexpr int N2 = L::N2, N3 = L::N3, Q2 = L::Q2, Q3 = L::Q3, NQ = L::NQ;
@@ -183,22 +183,22 @@ __global__ void __launch_bounds__(128, (N <= 4 ? 4 : (Nq <= 6 ? 3 : 2))) d4b_app
     const double *Ge = A.G + 6 * sl.quad_off;
     for (int t = lane; t < Q2; t += 32) { /* along r: lines (b,c); metric; transposed r-contraction in registers */
       const int b = t % Nq, c = t / Nq;
-      double Gv[6][Nq];
-#pragma unroll
-      for (int k = 0; k < 6; k++)
-#pragma unroll
-        for (int a = 0; a < Nq; a++) Gv[k][a] = __ldg(Ge + k * Q3 + Nq * t + a);
       double x[N], gr[Nq], gs[Nq], gt[Nq];
       const int o = BS * b + N * c;
+      const double *Gt = Ge + Nq * t;
       hld<N>(V2 + o, 1, x); hmat<N, Nq, false>(C, x, gr);
       hld<N>(V3 + o, 1, x); hmat<N, Nq, false>(B, x, gs);
       hld<N>(V4 + o, 1, x); hmat<N, Nq, false>(B, x, gt);
+      /* the metric is loaded point by point (six values live at a time instead of 6 Nq): the register budget of
+       * the instance, and with it the number of resident warps, is set by this loop */
 #pragma unroll
       for (int a = 0; a < Nq; a++) {
+        const double G00 = __ldg(Gt + a), G01 = __ldg(Gt + Q3 + a), G02 = __ldg(Gt + 2 * Q3 + a),
+                     G11 = __ldg(Gt + 3 * Q3 + a), G12 = __ldg(Gt + 4 * Q3 + a), G22 = __ldg(Gt + 5 * Q3 + a);
         const double g0 = gr[a], g1 = gs[a], g2 = gt[a];
-        gr[a] = Gv[0][a] * g0 + Gv[1][a] * g1 + Gv[2][a] * g2;
-        gs[a] = Gv[1][a] * g0 + Gv[3][a] * g1 + Gv[4][a] * g2;
-        gt[a] = Gv[2][a] * g0 + Gv[4][a] * g1 + Gv[5][a] * g2;
+        gr[a] = G00 * g0 + G01 * g1 + G02 * g2;
+        gs[a] = G01 * g0 + G11 * g1 + G12 * g2;
+        gt[a] = G02 * g0 + G12 * g1 + G22 * g2;
       }
       hmat<Nq, N, true>(C, gr, x); hst<N>(V2 + o, 1, x);
       hmat<Nq, N, true>(B, gs, x); hst<N>(V3 + o, 1, x);

@@ -23,8 +23,9 @@ def split_ranges(n_elem, nranks):
     return np.asarray(cuts, dtype=np.int64)
 
 
-def partition(fx, nranks, cuts=None):
-    """Return a list of per-rank table dicts (same keys as a fixture, plus 'owned', 'ghost_gid')."""
+def partition(fx, nranks, cuts=None, only=None):
+    """Return a list of per-rank table dicts (same keys as a fixture, plus 'owned', 'ghost_gid'); with only = r the
+    list holds None for the other ranks (each process of an N-rank run builds just its own tables)."""
     nl, ng, qt, _ = [int(v) for v in fx["hdr"]]
     assert ng == 0, "partition() expects serial tables"
     cuts = split_ranges(nl, nranks) if cuts is None else np.asarray(cuts, dtype=np.int64)
@@ -33,6 +34,9 @@ def partition(fx, nranks, cuts=None):
     owner = np.searchsorted(cuts, np.arange(nl), side="right") - 1
     parts = []
     for r in range(nranks):
+        if only is not None and r != only:
+            parts.append(None)
+            continue
         e0, e1 = int(cuts[r]), int(cuts[r + 1])
         recs = hm[hb[e0]:hb[e1]].copy()
         nbr = recs["nbr"].astype(np.int64)
@@ -135,3 +139,73 @@ def exchange_halo_torch(part, u_local, dist):
         for w in dist.batch_isend_irecv(ops):
             w.wait()
     return ug.numpy()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# multigrid hierarchy: d4est keeps families together when it partitions (p4est_partition(p4est, 1, NULL),
+# driver.c:135-152) so that restriction / prolongation stay rank-local, and drops the coarsest levels as the rank
+# count grows (Solver/d4est_solver_multigrid.c:253-277).  The same here: cuts are chosen on a base level and every
+# finer level is cut at the first descendant of the base cut elements.
+def hierarchy_cuts(levels, tabs, nranks, base=0):
+    """levels[l]: serial tables of level l (0 = coarsest), tabs[l]: transfer table between l and l+1.
+    Returns cuts[l] (element indices, length nranks+1) for l >= base; the base level is cut so that the FINEST-level
+    nodes below each range are balanced."""
+    top = len(levels) - 1
+    # first fine element of every coarse element, level by level
+    first_child = []
+    for l in range(top):
+        no_f = levels[l + 1]["node_off"][:int(levels[l + 1]["hdr"][0]) + 1]
+        fc = np.searchsorted(no_f, tabs[l]["child_off"][0::8]).astype(np.int64)
+        first_child.append(np.concatenate([fc, [int(levels[l + 1]["hdr"][0])]]))
+    nb = int(levels[base]["hdr"][0])
+    # finest-level nodes below each base element
+    lo = np.arange(nb + 1, dtype=np.int64)
+    for l in range(base, top):
+        lo = first_child[l][lo]
+    no_top = levels[top]["node_off"]
+    weight = np.diff(no_top[lo])
+    cum = np.concatenate([[0], np.cumsum(weight)])
+    cuts_b = [0]
+    for r in range(1, nranks):
+        c = int(np.searchsorted(cum, cum[-1] * r / nranks))
+        cuts_b.append(min(max(c, cuts_b[-1] + 1), nb - (nranks - r)))
+    cuts_b.append(nb)
+    cuts = {base: np.asarray(cuts_b, dtype=np.int64)}
+    for l in range(base, top):
+        cuts[l + 1] = first_child[l][cuts[l]]
+    return cuts
+
+
+def partition_transfer(tab, coarse, fine, r):
+    """Rows of a transfer table that belong to rank r, offsets re-based to the rank's node ranges.
+    coarse / fine: the rank-local tables of the two levels (from partition())."""
+    e0, e1 = coarse["owned"]
+    c0, f0 = coarse["node_range"][0], fine["node_range"][0]
+    ch = tab["child_off"][8 * e0:8 * e1].astype(np.int64).copy()
+    kind = tab["kind"][e0:e1]
+    used = np.zeros(ch.size, bool)
+    used[0::8] = True
+    for c in range(1, 8):
+        used[c::8] = kind == 1
+    ch[used] -= f0
+    ch[~used] = 0
+    return {"kind": kind.astype(np.int32).copy(), "degH": tab["degH"][e0:e1].astype(np.int32).copy(),
+            "coarse_off": (tab["coarse_off"][e0:e1] - c0).astype(np.int64),
+            "child_deg": tab["child_deg"][8 * e0:8 * e1].astype(np.int32).copy(), "child_off": ch}
+
+
+def partition_hierarchy(levels, tabs, nranks, base=0, only=None):
+    """Per rank: (list of rank-local level tables for levels base..top, list of rank-local transfer tables);
+    with only = r the other entries are None."""
+    cuts = hierarchy_cuts(levels, tabs, nranks, base)
+    top = len(levels) - 1
+    parts = {l: partition(levels[l], nranks, cuts[l], only) for l in range(base, top + 1)}
+    out = []
+    for r in range(nranks):
+        if only is not None and r != only:
+            out.append(None)
+            continue
+        lv = [parts[l][r] for l in range(base, top + 1)]
+        tr = [partition_transfer(tabs[l], parts[l][r], parts[l + 1][r], r) for l in range(base, top)]
+        out.append((lv, tr))
+    return out
