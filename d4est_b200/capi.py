@@ -98,6 +98,10 @@ SYMBOLS = {
     "d4b_residual_dev": (C.c_int, [_P, _P, _P, _P, _P]),
     "d4b_residual_host": (C.c_int, [_P, _P, _P, _P]),
     "d4b_cheby_smooth_host": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.POINTER(C.c_double)]),
+    "d4b_mass_set_coef": (C.c_int, [_P, _P]),
+    "d4b_mass_apply_dev": (C.c_int, [_P, _P, _P, C.c_int, _P]),
+    "d4b_mass_apply_host": (C.c_int, [_P, _P, _P, C.c_int]),
+    "d4b_apply_jac_dev": (C.c_int, [_P, _P, _P, _P]),
     "d4b_mg_pc_apply_host": (C.c_int, [_P, _P, _P]),
     "d4b_mg_fcg_solve_host": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_double)]),
     "d4b_mg_fcg_solve": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_double), _P, _P]),

@@ -59,7 +59,19 @@ int d4b_device_count(int *count)
   if (e != cudaSuccess) { n = 0; cudaGetLastError(); }
   *count = n; return D4B_OK;
 }
-int d4b_set_device(int dev) { D4B_CUDA(cudaSetDevice(dev)); return D4B_OK; }
+/* One device per process (one p4est rank = one GPU): the 1-D table pools, the per-instance __constant__ tables and
+ * the function attributes are cached per process, so a second device in the same process is refused. */
+static int g_device = -1;
+int d4b_set_device(int dev)
+{
+  if (g_device >= 0 && dev != g_device) {
+    d4b_set_error("d4b_set_device(%d): this process is already bound to device %d (one rank = one GPU)", dev, g_device);
+    return D4B_EINVAL;
+  }
+  D4B_CUDA(cudaSetDevice(dev));
+  g_device = dev;
+  return D4B_OK;
+}
 
 int d4b_dev_alloc(size_t bytes, void **p) { D4B_CUDA(cudaMalloc(p, bytes ? bytes : 8)); return D4B_OK; }
 int d4b_dev_free(void *p) { D4B_CUDA(cudaFree(p)); return D4B_OK; }
@@ -169,6 +181,7 @@ int d4b_mesh_create(const d4b_mesh_desc_t *D, d4b_mesh_t **out)
     if (D->degq[e] < 0 || D->degq[e] > D4B_MAX_DEGQ) { d4b_set_error("degq[%d] out of range", e); free(m); return D4B_EINVAL; }
     if (D->deg[e] > m->max_deg) m->max_deg = D->deg[e];
     if (D->degq[e] > m->max_degq) m->max_degq = D->degq[e];
+    if (D->degq[e] > m->max_degq_own) m->max_degq_own = D->degq[e];
     int64_t N = D->deg[e] + 1, Nq = D->degq[e] + 1;
     alg += 16 * N * N * N + 48 * Nq * Nq * Nq;
   }
@@ -231,7 +244,7 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
 {
   if (!m) return;
   cudaFree(m->deg); cudaFree(m->node_off); cudaFree(m->degq); cudaFree(m->quad_off); cudaFree(m->G);
-  cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost);
+  cudaFree(m->hm_begin); cudaFree(m->hm); cudaFree(m->fac); cudaFree(m->bc_g); cudaFree(m->u_ghost); cudaFree(m->mass_coef);
   cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->host_work); cudaFree(m->sc); cudaFree(m->dot_part); if (m->sc_h) cudaFreeHost(m->sc_h); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
   for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); cudaFree(m->fast[i].nrec); cudaFree(m->fast[i].v3_slots); }
   for (int i = 0; i < m->n_hp; i++) { cudaFree(m->hp[i].slots); cudaFree(m->hp[i].recs); }

@@ -234,12 +234,82 @@ d4b_apply_generic_kernel(const d4b_gen_args A)
   for (int i = threadIdx.x; i < N3; i += blockDim.x) Aue[i] = acc[i];
 }
 
+/* ---- mass-type term of apply_jac / build_residual: out (+)= I^T diag(w (x) w (x) w * c) I v per element, c given at the
+ * volume quadrature points (c = J f(x, u0): d4est_quadrature_apply_fofufofvlilj, Quadrature/d4est_quadrature.c:593-760,
+ * which ends in d4est_quadrature_apply_mass_matrix; with f = 1 the plain mass matrix of
+ * d4est_laplacian_build_rhs_with_strong_bc).  Element-local, no faces: one CTA per element, run-time sizes. */
+struct d4b_mass_args {
+  const int32_t *deg; const int64_t *node_off; const int32_t *degq; const int64_t *quad_off;
+  const double *coef, *v; double *out; int n_local, qt, NX, NQX, accumulate;
+};
+extern "C" __global__ void __launch_bounds__(128) d4b_mass_kernel(const d4b_mass_args A)
+{
+  extern __shared__ double sm[];
+  const int e = blockIdx.x;
+  if (e >= A.n_local) return;
+  const d4b_ops_dev &ops = c_ops[A.qt];
+  const double *pool = ops.pool;
+  const int dg = A.deg[e], dq = A.degq[e], N = dg + 1, Nq = dq + 1, N3 = N * N * N, Nq3 = Nq * Nq * Nq;
+  const int MX3 = (A.NX > A.NQX ? A.NX : A.NQX); 
+  double *t1 = sm, *t2 = sm + MX3 * MX3 * MX3;
+  const double *I = pool + ops.idx.I[dg][dq][0], *wq = pool + ops.idx.w[dq];
+  const double *ve = A.v + A.node_off[e], *ce = A.coef + A.quad_off[e];
+  for (int i = threadIdx.x; i < N3; i += blockDim.x) t1[i] = ve[i];
+  __syncthreads();
+  contract(I, N, 1, Nq, N, t1, t2, N, N, N, 0, false);
+  contract(I, N, 1, Nq, N, t2, t1, Nq, N, N, 1, false);
+  contract(I, N, 1, Nq, N, t1, t2, Nq, Nq, N, 2, false);
+  for (int q = threadIdx.x; q < Nq3; q += blockDim.x) {
+    const int a = q % Nq, b = (q / Nq) % Nq, c = q / (Nq * Nq);
+    t2[q] *= wq[a] * wq[b] * wq[c] * ce[q];
+  }
+  __syncthreads();
+  contract(I, 1, N, N, Nq, t2, t1, Nq, Nq, Nq, 2, false);
+  contract(I, 1, N, N, Nq, t1, t2, Nq, Nq, N, 1, false);
+  contract(I, 1, N, N, Nq, t2, t1, Nq, N, N, 0, false);
+  double *oe = A.out + A.node_off[e];
+  for (int i = threadIdx.x; i < N3; i += blockDim.x) oe[i] = A.accumulate ? oe[i] + t1[i] : t1[i];
+}
+
 size_t d4b_generic_smem_bytes(int NX, int NQX)
 {
   int MX = NX > NQX ? NX : NQX;
   size_t n = (size_t)5 * NX * NX * NX + (size_t)3 * NQX * NQX * NQX + (size_t)2 * MX * MX * MX;
   n += (size_t)4 * (2 * NX * NX + 3 * NQX * NQX + NQX * MX);
   return n * sizeof(double);
+}
+
+static int generic_bind_ops(int qt);
+
+int d4b_launch_mass(const d4b_mesh *m, const double *coef, const double *v, double *out, int accumulate, cudaStream_t st)
+{
+  int rc = generic_bind_ops(m->quad_type); if (rc) return rc;
+  if (m->n_local == 0) return D4B_OK;
+  d4b_mass_args A;
+  A.deg = m->deg; A.node_off = m->node_off; A.degq = m->degq; A.quad_off = m->quad_off; A.coef = coef; A.v = v; A.out = out;
+  A.n_local = m->n_local; A.qt = m->quad_type; A.NX = m->max_deg + 1; A.NQX = m->max_degq_own + 1; A.accumulate = accumulate;
+  const int MX = A.NX > A.NQX ? A.NX : A.NQX;
+  const size_t smem = 2 * (size_t)MX * MX * MX * sizeof(double);
+  static size_t attr = 0;
+  if (smem > 48 * 1024 && smem > attr) {
+    D4B_CUDA(cudaFuncSetAttribute(d4b_mass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = smem;
+  }
+  d4b_mass_kernel<<<m->n_local, 128, smem, st>>>(A);
+  D4B_CUDA(cudaGetLastError());
+  d4b_count_launch(1);
+  return D4B_OK;
+}
+
+static int generic_bind_ops(int qt)
+{
+  static bool bound[2] = {false, false};
+  if (bound[qt]) return D4B_OK;
+  const d4b_ops_dev *ops = d4b_ops_device(qt);
+  if (!ops) return D4B_ECUDA;
+  D4B_CUDA(cudaMemcpyToSymbol(c_ops, ops, sizeof(d4b_ops_dev), qt * sizeof(d4b_ops_dev), cudaMemcpyHostToDevice));
+  D4B_CUDA(cudaDeviceSynchronize());
+  bound[qt] = true;
+  return D4B_OK;
 }
 
 int d4b_launch_generic(const d4b_mesh *m, const double *u, double *Au, const int32_t *elem_list,
@@ -251,15 +321,7 @@ int d4b_launch_generic(const d4b_mesh *m, const double *u, double *Au, const int
                                   227 * 1024));
     attr_set = true;
   }
-  static bool bound[2] = {false, false};
-  if (!bound[m->quad_type]) { /* 1-D tables: built once on the host, resident afterwards */
-    const d4b_ops_dev *ops = d4b_ops_device(m->quad_type);
-    if (!ops) return D4B_ECUDA;
-    D4B_CUDA(cudaMemcpyToSymbol(c_ops, ops, sizeof(d4b_ops_dev), m->quad_type * sizeof(d4b_ops_dev),
-                                cudaMemcpyHostToDevice));
-    D4B_CUDA(cudaDeviceSynchronize());
-    bound[m->quad_type] = true;
-  }
+  { int rcb = generic_bind_ops(m->quad_type); if (rcb) return rcb; }
   d4b_gen_args A;
   A.deg = m->deg; A.node_off = m->node_off; A.degq = m->degq; A.quad_off = m->quad_off; A.G = m->G;
   A.hm_begin = m->hm_begin; A.hm = m->hm; A.fac = m->fac; A.bc_g = m->bc_g;

@@ -61,4 +61,42 @@ int d4b_cheby_smooth_host(d4b_mesh_t *m, double *u_host, const double *rhs_host,
   return D4B_OK;
 }
 
+
+/* ---- mass-type terms of apply_jac / build_residual: Au += M_c v with
+ *      M_c = I^T diag(w J f(x, u0)) I, the operator d4est_quadrature_apply_fofufofvlilj applies element by element
+ *      (Quadrature/d4est_quadrature.c:593; caller e.g. Problems/ConstantDensityStar/constant_density_star_fcns.h:484-605).
+ *      The coefficient c = J f(x, u0) at the volume quadrature points changes only with the linearisation point: it
+ *      is set once (host array of quad_off[n_local] doubles in element order) and stays resident. */
+int d4b_mass_set_coef(d4b_mesh_t *m, const double *coef_quad_host)
+{
+  if (!coef_quad_host) { cudaFree(m->mass_coef); m->mass_coef = nullptr; return D4B_OK; }
+  if (!m->mass_coef) D4B_CUDA(cudaMalloc((void **)&m->mass_coef, (size_t)(m->total_quad ? m->total_quad : 1) * sizeof(double)));
+  D4B_CUDA(cudaMemcpy(m->mass_coef, coef_quad_host, (size_t)m->total_quad * sizeof(double), cudaMemcpyHostToDevice));
+  return D4B_OK;
+}
+int d4b_mass_apply_dev(d4b_mesh_t *m, const double *v_dev, double *out_dev, int accumulate, void *stream)
+{
+  if (!m->mass_coef) { d4b_set_error("d4b_mass_apply: no coefficient set (d4b_mass_set_coef)"); return D4B_EINVAL; }
+  return d4b_launch_mass(m, m->mass_coef, v_dev, out_dev, accumulate, (cudaStream_t)stream);
+}
+/* Au = A u + M_c u: the Jacobian apply of a semilinear problem (Laplacian + f'(u0) mass term) in one call */
+int d4b_apply_jac_dev(d4b_mesh_t *m, const double *u_dev, double *Au_dev, void *stream)
+{
+  int rc = d4b_apply_dev(m, u_dev, Au_dev, stream);
+  if (rc != D4B_OK) return rc;
+  return d4b_mass_apply_dev(m, u_dev, Au_dev, 1, stream);
+}
+int d4b_mass_apply_host(d4b_mesh_t *m, const double *v_host, double *out_host, int accumulate)
+{
+  int rc = ensure_host_work(m); if (rc) return rc;
+  const int64_t n = m->local_nodes; const size_t nb = (size_t)n * sizeof(double);
+  double *v = m->host_work, *o = v + n;
+  D4B_CUDA(cudaMemcpyAsync(v, v_host, nb, cudaMemcpyHostToDevice, m->stream));
+  if (accumulate) D4B_CUDA(cudaMemcpyAsync(o, out_host, nb, cudaMemcpyHostToDevice, m->stream));
+  if ((rc = d4b_mass_apply_dev(m, v, o, accumulate, m->stream)) != D4B_OK) return rc;
+  D4B_CUDA(cudaMemcpyAsync(out_host, o, nb, cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  return D4B_OK;
+}
+
 } /* extern C */

@@ -40,11 +40,12 @@ struct d4b_hp_bucket {
 
 /* device-resident mesh level */
 struct d4b_mesh {
-  int n_local, n_ghost, quad_type, max_deg, max_degq, max_deg_ext;
+  int n_local, n_ghost, quad_type, max_deg, max_degq, max_deg_ext, max_degq_own;
   int64_t local_nodes, ghost_nodes, total_quad, n_hm, n_fac, n_bc_g;
   int32_t *deg; int64_t *node_off; int32_t *degq; int64_t *quad_off;
   double *G; int32_t *hm_begin; d4b_hm_t *hm; double *fac; double *bc_g;
   double *u_ghost;                 /* [ghost_nodes] received halo                        */
+  double *mass_coef;               /* [total_quad] coefficient of the mass-type term (d4b_mass_set_coef), or NULL */
   int ghost_supplied;              /* d4b_set_ghost_host was called (single-process tests of the N > 1 layout) */
   double *u_stage, *Au_stage;      /* staging for d4b_apply_host                         */
   double *sc, *dot_part, *sc_h;    /* device scalar block, reduction partials, pinned host mirror (d4b_solver.cu) */
@@ -107,6 +108,7 @@ int d4b_norm2_dev(d4b_mesh *m, const double *r, cudaStream_t st);
 int d4b_read_r2(d4b_mesh *m, double *r2, cudaStream_t st);
 int d4b_allreduce_sum_dev(double *dev, int k, cudaStream_t st);
 int d4b_mesh_make_streams(d4b_mesh *m);
+int d4b_launch_mass(const d4b_mesh *m, const double *coef, const double *v, double *out, int accumulate, cudaStream_t st);
 
 #define D4B_CUDA(call)                                                                   \
   do { cudaError_t e_ = (call);                                                          \

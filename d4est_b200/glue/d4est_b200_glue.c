@@ -603,3 +603,51 @@ void d4est_b200_laplacian_build_rhs_with_strong_bc(p4est_t *p4est, d4est_ghost_t
   P4EST_FREE(u0); P4EST_FREE(Au0); P4EST_FREE(f);
   (void)ghost_data; (void)which_field;
 }
+
+/* ---------------------------------------------------------------- mass-type terms
+ * c = J f(x, u0) at the volume quadrature points, tabulated once per linearisation point with the user's own
+ * callback exactly as d4est_quadrature_apply_fofufofvlilj does per element (Quadrature/d4est_quadrature.c:629-683,
+ * interpolate_f = 0): u0 is interpolated to the quadrature points, f is evaluated there.  The device then applies
+ * I^T diag(w c) I (the d4est_quadrature_apply_mass_matrix the reference ends in, :735-750) for every element at once. */
+void d4est_b200_mass_set_fofu(p4est_t *p4est, d4est_ghost_t *ghost, d4est_laplacian_with_opt_flux_data_t *flux_data,
+                              d4est_operators_t *ops, d4est_geometry_t *geom, d4est_quadrature_t *quad,
+                              d4est_mesh_data_t *factors, double *u0, d4est_xyzu_fcn_t fofu_fcn, void *fofu_ctx)
+{
+  d4b_mesh_t *m = d4est_b200_level_get(p4est, ghost, flux_data, ops, geom, quad, factors);
+  size_t nq_total = 0;
+  for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+    sc_array_t *tq = &p4est_tree_array_index(p4est->trees, tt)->quadrants;
+    for (size_t q = 0; q < tq->elem_count; ++q)
+      nq_total += (size_t)d4est_lgl_get_nodes(3, ((d4est_element_data_t *)p4est_quadrant_array_index(tq, q)->p.user_data)->deg_quad);
+  }
+  double *coef = P4EST_ALLOC(double, nq_total ? nq_total : 1);
+  double uq[D4B_OPS_MAXN * D4B_OPS_MAXN * D4B_OPS_MAXN];
+  for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+    sc_array_t *tq = &p4est_tree_array_index(p4est->trees, tt)->quadrants;
+    for (size_t q = 0; q < tq->elem_count; ++q) {
+      d4est_element_data_t *ed = (d4est_element_data_t *)p4est_quadrant_array_index(tq, q)->p.user_data;
+      int n3 = d4est_lgl_get_nodes(3, ed->deg_quad);
+      d4est_quadrature_volume_t mo;
+      mo.dq = ed->dq; mo.tree = ed->tree; mo.q[0] = ed->q[0]; mo.q[1] = ed->q[1]; mo.q[2] = ed->q[2]; mo.element_id = ed->id;
+      d4est_mesh_data_on_element_t md = d4est_mesh_data_on_element(factors, ed);
+      double *J = d4est_mesh_get_jacobian_on_quadrature_points(factors, ed);
+      if (u0)
+        d4est_quadrature_interpolate(ops, quad, geom, &mo, QUAD_OBJECT_VOLUME, QUAD_INTEGRAND_UNKNOWN,
+                                     &u0[ed->nodal_stride], ed->deg, uq, ed->deg_quad);
+      double *c = &coef[ed->quad_stride];
+      for (int i = 0; i < n3; i++)
+        c[i] = J[i] * (fofu_fcn ? fofu_fcn(md.xyz_quad[0][i], md.xyz_quad[1][i], md.xyz_quad[2][i], u0 ? uq[i] : 0., fofu_ctx) : 1.);
+    }
+  }
+  check_rc(d4b_mass_set_coef(m, coef), "mass coefficient");
+  P4EST_FREE(coef);
+}
+
+/* vecs->Au += M_c vecs->u: the loop over elements of e.g. constant_density_star_fcns.h:540-603 in one device call */
+void d4est_b200_mass_apply_add(p4est_t *p4est, d4est_ghost_t *ghost, d4est_laplacian_with_opt_flux_data_t *flux_data,
+                               d4est_elliptic_data_t *vecs, d4est_operators_t *ops, d4est_geometry_t *geom,
+                               d4est_quadrature_t *quad, d4est_mesh_data_t *factors)
+{
+  d4b_mesh_t *m = d4est_b200_level_get(p4est, ghost, flux_data, ops, geom, quad, factors);
+  check_rc(d4b_mass_apply_host(m, vecs->u, vecs->Au, 1), "mass apply");
+}

@@ -27,7 +27,9 @@ extern "C" {
 #endif
 
 #define D4B_MAX_DEG 11      /* N  <= 12 */
-#define D4B_MAX_DEGQ 15     /* Nq <= 16 */
+#define D4B_MAX_DEGQ 15     /* Nq <= 16; the completeness kernel additionally needs its scratch of one element to fit
+                               227 KB of shared memory (d4b_mesh_create reports it: e.g. deg 11 with deg_quad >= 14
+                               does not).  Template instances exist for deg 1..7, deg_quad = deg..deg+3. */
 
 enum { D4B_OK = 0, D4B_EINVAL = 1, D4B_ECUDA = 2, D4B_ENOMEM = 3, D4B_ENCCL = 4, D4B_ENODEV = 5 };
 
@@ -101,7 +103,7 @@ typedef struct d4b_mesh d4b_mesh_t; /* opaque: device-resident level */
 
 const char *d4b_last_error(void);
 int d4b_device_count(int *count);
-int d4b_set_device(int dev);
+int d4b_set_device(int dev);   /* one device per process: a second, different device is refused */
 const char *d4b_version(void);
 
 /* ---- mesh residency (hook: d4est_mesh_update, Mesh/d4est_mesh.c:2790) ------------ */
@@ -239,6 +241,13 @@ int d4b_residual_host(d4b_mesh_t *m, const double *u_host, const double *rhs_hos
 int d4b_cheby_smooth_host(d4b_mesh_t *m, double *u_host, const double *rhs_host, double *r_host, int cheby_imax,
                           int eigs_cg_imax, double lmax_lmin_ratio, double max_multiplier, int use_new_cg_eigs,
                           int compute_eig, double *eig);
+/* mass-type terms of apply_jac / build_residual: out (+)= I^T diag(w c) I v with c = J f(x, u0) at the volume
+ * quadrature points (d4est_quadrature_apply_fofufofvlilj, Quadrature/d4est_quadrature.c:593; f = 1:
+ * d4est_quadrature_apply_mass_matrix :776).  The coefficient is resident until it is set again. */
+int d4b_mass_set_coef(d4b_mesh_t *m, const double *coef_quad_host);
+int d4b_mass_apply_dev(d4b_mesh_t *m, const double *v_dev, double *out_dev, int accumulate, void *cuda_stream);
+int d4b_mass_apply_host(d4b_mesh_t *m, const double *v_host, double *out_host, int accumulate);
+int d4b_apply_jac_dev(d4b_mesh_t *m, const double *u_dev, double *Au_dev, void *cuda_stream);   /* A u + M_c u */
 int d4b_mg_pc_apply_host(d4b_mg_t *g, const double *r_host, double *z_host);
 int d4b_mg_fcg_solve_host(d4b_mg_t *g, double *u_host, const double *rhs_host, int imax, double atol, double rtol,
                           int *iters, double *final_res);

@@ -83,6 +83,16 @@ void d4est_b200_laplacian_build_rhs_with_strong_bc(p4est_t *p4est, d4est_ghost_t
                                                    double *rhs, d4est_xyz_fcn_t problem_rhs_fcn,
                                                    d4est_mesh_init_field_option_t init_option, void *ctx, int which_field);
 
+/* Mass-type terms of apply_jac / build_residual (d4est_quadrature_apply_fofufofvlilj, Quadrature/d4est_quadrature.c:593;
+ * callers e.g. Problems/ConstantDensityStar/constant_density_star_fcns.h:484-605): the coefficient J f(x, u0) is
+ * tabulated once per linearisation point with the user's callback; Au += M_c u is then one device call. */
+void d4est_b200_mass_set_fofu(p4est_t *p4est, d4est_ghost_t *ghost, d4est_laplacian_with_opt_flux_data_t *flux_data,
+                              d4est_operators_t *ops, d4est_geometry_t *geom, d4est_quadrature_t *quad,
+                              d4est_mesh_data_t *factors, double *u0, d4est_xyzu_fcn_t fofu_fcn, void *fofu_ctx);
+void d4est_b200_mass_apply_add(p4est_t *p4est, d4est_ghost_t *ghost, d4est_laplacian_with_opt_flux_data_t *flux_data,
+                               d4est_elliptic_data_t *vecs, d4est_operators_t *ops, d4est_geometry_t *geom,
+                               d4est_quadrature_t *quad, d4est_mesh_data_t *factors);
+
 /* ------------------------------------------------------------------ solver interfaces (d4est_b200_solver_glue.c)
  * Compiled only where d4est's Solver/ headers are on the include path (define D4EST_B200_NO_SOLVER_GLUE to skip). */
 #ifndef D4EST_B200_NO_SOLVER_GLUE

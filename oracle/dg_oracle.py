@@ -196,3 +196,19 @@ def apply(fx, u, u_ghost=None):
                np.einsum("ij,isr->jsr", D, W3[2])).reshape(-1)
         Au[node_off[e]:node_off[e + 1]] = acc + out
     return Au
+
+
+def mass_apply(fx, coef, v):
+    """out = I^T diag(w (x) w (x) w * c) I v per element, c = J f(x, u0) at the volume quadrature points: what
+    d4est_quadrature_apply_fofufofvlilj computes element by element (Quadrature/d4est_quadrature.c:593-760, ending in
+    d4est_quadrature_apply_mass_matrix).  Pinned against the reference's own output (fixture key mass_ref)."""
+    nl, _, qt, _ = [int(x) for x in fx["hdr"]]
+    no, qo = fx["node_off"], fx["quad_off"]
+    out = np.zeros(int(no[nl]))
+    for e in range(nl):
+        dg, dq = int(fx["deg"][e]), int(fx["degq"][e]); N, Nq = dg + 1, dq + 1
+        I = interp(dg, dq, qt); _, w = quad_rule(dq, qt)
+        vq = np.einsum("at,bs,cr,tsr->abc", I, I, I, v[no[e]:no[e + 1]].reshape(N, N, N))
+        c = coef[qo[e]:qo[e + 1]].reshape(Nq, Nq, Nq) * np.einsum("a,b,c->abc", w, w, w)
+        out[no[e]:no[e + 1]] = np.einsum("at,bs,cr,abc->tsr", I, I, I, c * vq).reshape(-1)
+    return out

@@ -45,6 +45,10 @@ static double robin_coeff_base(double x, double y, double z, void *user, d4est_l
 static double robin_rhs_base(double x, double y, double z, void *user, d4est_laplacian_flux_boundary_data_t *bd, int i)
 { return robin_rhs_opt(x, y, z, user, NULL, i); }
 
+/* coefficient of the mass-type term test: a smooth function of position and of the linearisation point */
+static double test_fofu(double x, double y, double z, double u, void *ctx)
+{ (void)ctx; return 1. + 0.5 * x - 0.25 * y * z + u * u / (1. + u * u); }
+
 static void ref_apply_lhs(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost_data_t *gd, d4est_elliptic_data_t *v,
                           d4est_operators_t *ops, d4est_geometry_t *geom, d4est_quadrature_t *quad,
                           d4est_mesh_data_t *factors, void *user)
@@ -154,6 +158,34 @@ int main(int argc, char **argv)
     fix_write(f, "u", FIX_F64, n, u);
     fix_write(f, "Au_ref_baseline", FIX_F64, n, Au0);
     fix_write(f, "Au_ref_with_opt", FIX_F64, n, Au1);
+    { /* mass-type term: the reference's d4est_quadrature_apply_fofufofvlilj element by element (u0 = u, vec = u),
+         and the coefficient table J f(x, u0) it is equivalent to */
+      double *mref = P4EST_ALLOC_ZERO(double, n);
+      int64_t nqt = D->quad_off[D->n_local];
+      double *coef = P4EST_ALLOC(double, nqt), *uq = P4EST_ALLOC(double, 32 * 32 * 32);
+      for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+        sc_array_t *tq = &p4est_tree_array_index(p4est->trees, tt)->quadrants;
+        for (size_t q = 0; q < tq->elem_count; ++q) {
+          d4est_element_data_t *ed = (d4est_element_data_t *)p4est_quadrant_array_index(tq, q)->p.user_data;
+          d4est_quadrature_volume_t mo;
+          mo.dq = ed->dq; mo.tree = ed->tree; mo.q[0] = ed->q[0]; mo.q[1] = ed->q[1]; mo.q[2] = ed->q[2]; mo.element_id = ed->id;
+          d4est_mesh_data_on_element_t md = d4est_mesh_data_on_element(factors, ed);
+          double *J = d4est_mesh_get_jacobian_on_quadrature_points(factors, ed);
+          d4est_quadrature_apply_fofufofvlilj(ops, geom, quad, &mo, QUAD_OBJECT_VOLUME, QUAD_INTEGRAND_UNKNOWN,
+                                              &u[ed->nodal_stride], &u[ed->nodal_stride], NULL, ed->deg, md.xyz_quad, J,
+                                              ed->deg_quad, &mref[ed->nodal_stride], test_fofu, NULL, NULL, NULL,
+                                              QUAD_APPLY_MATRIX, 0, NULL);
+          int n3 = d4est_lgl_get_nodes(3, ed->deg_quad);
+          d4est_quadrature_interpolate(ops, quad, geom, &mo, QUAD_OBJECT_VOLUME, QUAD_INTEGRAND_UNKNOWN,
+                                       &u[ed->nodal_stride], ed->deg, uq, ed->deg_quad);
+          for (int i = 0; i < n3; i++)
+            coef[ed->quad_stride + i] = J[i] * test_fofu(md.xyz_quad[0][i], md.xyz_quad[1][i], md.xyz_quad[2][i], uq[i], NULL);
+        }
+      }
+      fix_write(f, "mass_coef", FIX_F64, nqt, coef);
+      fix_write(f, "mass_ref", FIX_F64, n, mref);
+      P4EST_FREE(mref); P4EST_FREE(coef); P4EST_FREE(uq);
+    }
     if (!getenv("D4B_HARNESS_NO_SOLVER")) { /* reference smoother pieces on the same operator: cg_eigs (Solver/d4est_solver_cg_eigs.c:115) from a
          zero guess with rhs = A u, then d4est_solver_multigrid_smoother_cheby_iterate_aux (:81) */
       double *su = P4EST_ALLOC_ZERO(double, n), *sAu = P4EST_ALLOC_ZERO(double, n), *sr = P4EST_ALLOC_ZERO(double, n);

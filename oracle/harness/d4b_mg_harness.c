@@ -46,6 +46,9 @@ static void ref_apply_lhs(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost_data
                           d4est_mesh_data_t *factors, void *user)
 { d4est_laplacian_with_opt_apply_aij(p4est, ghost, gd, v, (d4est_laplacian_with_opt_flux_data_t *)user, ops, geom, quad, factors, 0); }
 
+static double test_fofu(double x, double y, double z, double u, void *ctx)
+{ (void)ctx; return 1. + 0.5 * x - 0.25 * y * z + u * u / (1. + u * u); }
+
 static double now_s(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec + 1e-9 * t.tv_nsec; }
 static double nrm2(const double *a, int n) { double s = 0.; for (int i = 0; i < n; i++) s += a[i] * a[i]; return sqrt(s); }
 static double rel_l2(const double *a, const double *b, int n)
@@ -256,6 +259,31 @@ int main(int argc, char **argv)
     for (int i = 0; i < n; i++) y2[i] = rhs[i] - y0[i];
     double e_resid = 0.; { double s = 0.; for (int i = 0; i < n; i++) s += (y1[i] - y2[i]) * (y1[i] - y2[i]); e_resid = sqrt(s) / nrm2(y0, n); }
 
+    /* (a') the mass-type term: the reference's per-element d4est_quadrature_apply_fofufofvlilj loop against the glue
+     *      (coefficient tabulated with the same callback, one device call) */
+    double e_mass;
+    {
+      double *mref = P4EST_ALLOC_ZERO(double, n), *mdev = P4EST_ALLOC_ZERO(double, n);
+      for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+        sc_array_t *tq = &p4est_tree_array_index(p4est->trees, tt)->quadrants;
+        for (size_t q = 0; q < tq->elem_count; ++q) {
+          d4est_element_data_t *ed = (d4est_element_data_t *)p4est_quadrant_array_index(tq, q)->p.user_data;
+          d4est_quadrature_volume_t mo;
+          mo.dq = ed->dq; mo.tree = ed->tree; mo.q[0] = ed->q[0]; mo.q[1] = ed->q[1]; mo.q[2] = ed->q[2]; mo.element_id = ed->id;
+          d4est_mesh_data_on_element_t md = d4est_mesh_data_on_element(factors, ed);
+          d4est_quadrature_apply_fofufofvlilj(ops, geom, quad, &mo, QUAD_OBJECT_VOLUME, QUAD_INTEGRAND_UNKNOWN,
+                                              &ustar[ed->nodal_stride], &ustar[ed->nodal_stride], NULL, ed->deg, md.xyz_quad,
+                                              d4est_mesh_get_jacobian_on_quadrature_points(factors, ed), ed->deg_quad,
+                                              &mref[ed->nodal_stride], test_fofu, NULL, NULL, NULL, QUAD_APPLY_MATRIX, 0, NULL);
+        }
+      }
+      d4est_b200_mass_set_fofu(p4est, ghost, fl1, ops, geom, quad, factors, ustar, test_fofu, NULL);
+      d4est_elliptic_data_t vm; d4est_elliptic_data_copy_ptrs(&vecs, &vm); vm.u = ustar; vm.Au = mdev;
+      d4est_b200_mass_apply_add(p4est, ghost, fl1, &vm, ops, geom, quad, factors);
+      e_mass = rel_l2(mdev, mref, n);
+      P4EST_FREE(mref); P4EST_FREE(mdev);
+    }
+
     /* (b) the resident multigrid behind d4est_krylov_pc_t and d4est_solver_fcg_solve's argument list */
     d4est_b200_mg_t *G = d4est_b200_mg_capture(p4est, mg, fl1, &vecs);
     d4est_krylov_pc_t *pc_dev = d4est_b200_krylov_pc_multigrid_create(G);
@@ -280,12 +308,12 @@ int main(int argc, char **argv)
     double t_hyb = now_s() - t0;
     double e_hyb = rel_l2(y2, R.z0, n);
 
-    printf("{\"what\": \"gpu_check\", \"apply_lhs_rel_l2\": %.3e, \"baseline_twin_rel_l2\": %.3e, \"build_residual_rel_l2\": %.3e, "
+    printf("{\"what\": \"gpu_check\", \"apply_lhs_rel_l2\": %.3e, \"baseline_twin_rel_l2\": %.3e, \"build_residual_rel_l2\": %.3e, \"mass_term_rel_l2\": %.3e, "
            "\"pc_apply_resident_rel_l2\": %.3e, \"pc_apply_d4est_vcycle_device_smoother_rel_l2\": %.3e, "
            "\"fcg_iterations_reference\": %d, \"fcg_iterations_device\": %d, \"true_residual_reference\": %.6e, "
            "\"true_residual_device\": %.6e, \"seconds_reference_solve_cpu\": %.3f, \"seconds_device_solve\": %.4f, "
            "\"seconds_d4est_vcycle_device_smoother\": %.4f, \"kernel_launches\": %lld}\n",
-           e_apply, e_twin, e_resid, e_pc, e_hyb, it_ref, it_dev, res_ref, res_dev, t_ref, t_dev, t_hyb,
+           e_apply, e_twin, e_resid, e_mass, e_pc, e_hyb, it_ref, it_dev, res_ref, res_dev, t_ref, t_dev, t_hyb,
            (long long)d4b_kernel_launches());
     d4est_b200_krylov_pc_multigrid_destroy(pc_dev);
     d4est_b200_mg_destroy(G);

@@ -170,3 +170,31 @@ def test_reference_golden_numbers_on_the_device(ref_fixture_dir):
     fw = fixture.load(pw)
     Aw = d4est_b200.MeshLevel(fw).apply_host(fw["u"])
     assert abs(Aw[33010] - (-0.0034181705065613010)) < 1e-12
+
+
+@pytest.mark.parametrize("name", ["cubed_sphere_hp2", "cubed_sphere_hp_p7", "brick_p3_l3"])
+def test_mass_term_matches_reference(name, ref_fixture_dir):
+    """d4b_mass_apply (I^T diag(w J f(x, u0)) I v, coefficient resident) against the reference's
+    d4est_quadrature_apply_fofufofvlilj run element by element; and A u + M u in one call (d4b_apply_jac_dev)."""
+    from d4est_b200.capi import DevVec, lib, check
+    p = os.path.join(ref_fixture_dir, name + ".fix")
+    if not os.path.exists(p):
+        pytest.skip("reference fixture not built")
+    fx = fixture.load(p)
+    if "mass_ref" not in fx:
+        pytest.skip("fixture predates the mass-term reference")
+    lvl = d4est_b200.MeshLevel(fx)
+    coef = np.ascontiguousarray(fx["mass_coef"])
+    check(lib().d4b_mass_set_coef(lvl.handle, coef.ctypes.data_as(ctypes_voidp())))
+    out = np.zeros_like(fx["u"]); u = np.ascontiguousarray(fx["u"])
+    check(lib().d4b_mass_apply_host(lvl.handle, u.ctypes.data_as(ctypes_voidp()), out.ctypes.data_as(ctypes_voidp()), 0))
+    assert rel(out, fx["mass_ref"]) < TOL
+    U, V = DevVec(lvl.local_nodes, u), DevVec(lvl.local_nodes)
+    check(lib().d4b_apply_jac_dev(lvl.handle, U.ptr, V.ptr, None))
+    assert rel(V.get(), fx["Au_ref_with_opt"] + fx["mass_ref"]) < TOL
+    lvl.close()
+
+
+def ctypes_voidp():
+    import ctypes
+    return ctypes.c_void_p

@@ -117,6 +117,7 @@ def test_d4est_facing_entry_points_in_one_process_with_the_reference():
     chk = [o for o in out if o.get("what") == "gpu_check"][0]
     print(json.dumps(chk))
     assert chk["apply_lhs_rel_l2"] < 1e-12 and chk["baseline_twin_rel_l2"] < 1e-12 and chk["build_residual_rel_l2"] < 1e-12
+    assert chk["mass_term_rel_l2"] < 1e-12
     assert chk["pc_apply_resident_rel_l2"] < 1e-9
     assert chk["pc_apply_d4est_vcycle_device_smoother_rel_l2"] < 1e-9
     assert abs(chk["fcg_iterations_device"] - chk["fcg_iterations_reference"]) <= 1

@@ -170,3 +170,15 @@ def test_reference_golden_numbers_are_reproduced_by_the_oracle_build(ref_fixture
     assert abs(jw["Au_baseline_33010"] - (-0.0034181705065613010)) < 1e-12     # the reference test itself allows 1e-3
     fw = fixture.load(os.path.join(ref_fixture_dir, "wedge_consistency.fix"))
     assert fw["Au_ref_baseline"][33010] == jw["Au_baseline_33010"]
+
+
+def test_mass_term_oracle_matches_reference(ref_fixture_dir):
+    """dg_oracle.mass_apply against the reference's d4est_quadrature_apply_fofufofvlilj run element by element on the
+    curved hp mesh (mass-type term of apply_jac)."""
+    p = os.path.join(ref_fixture_dir, "cubed_sphere_hp2.fix")
+    if not os.path.exists(p):
+        pytest.skip("reference fixture not built")
+    fx = fixture.load(p)
+    if "mass_ref" not in fx:
+        pytest.skip("fixture predates the mass-term reference")
+    assert rel(dg_oracle.mass_apply(fx, fx["mass_coef"], fx["u"]), fx["mass_ref"]) < TOL
