@@ -130,7 +130,7 @@ __device__ __forceinline__ int hp_tcode_src(int tcode, int n, int a, int b)
 }
 
 template <int N, int Nq>
-__global__ void __launch_bounds__(128, (N <= 4 ? 6 : 5)) d4b_apply_hp_kernel(const hp_args A)
+__global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_apply_hp_kernel(const hp_args A)
 {
   using L = HL<N, Nq>;
   constexpr int N2 = L::N2, N3 = L::N3, Q2 = L::Q2, Q3 = L::Q3, NQ = L::NQ;
