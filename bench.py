@@ -381,6 +381,8 @@ def main():
     total_ms = ev[0].elapsed_time(ev[-1])
     per = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps))
     clocks = sampler.summary(t_begin, t_end)
+    if os.environ.get("D4B_BENCH_RANK_TIMES"):
+        print(f"[bench] rank {rank}: {total_ms / args.steps:.4f} ms per step, median {per[len(per) // 2]:.4f}", file=sys.stderr, flush=True)
     tmax = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)

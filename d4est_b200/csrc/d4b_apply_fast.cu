@@ -78,21 +78,34 @@ template <int n> __device__ __forceinline__ void st(double *p, int s, const doub
   for (int i = 0; i < n; i++) p[i * s] = x[i];
 }
 
+/* Shared-memory paddings of one instance.  The defaults are the hand-chosen round-1 strides; the specialisations
+ * in d4b_fast_pads.inc come from tools/fast_bank_sim.py, a bank-conflict model of every shared access of the
+ * kernel (threads of N*N-wide elements straddle half-warps, so the best strides are not the obvious odd ones).
+ * Measured at p = 4 (ncu, 32^3 brick): shared wavefronts 52.1 M -> 41.4 M, 323.6 -> 305.9 us. */
+template <int N, int Nq> struct fast_pad {
+  static constexpr int SJ = N + 1, AS = N * N + (N == 4 ? 4 : 0), BS = N * Nq + 1, TB = N * N + 1, QP = Nq * Nq, PP = 0;
+};
+#define FAST_PAD(n, q, sj, as, bs, tb, qp, pp)                                                      \
+  template <> struct fast_pad<n, q> { static constexpr int SJ = sj, AS = as, BS = bs, TB = tb, QP = qp, PP = pp; };
+#include "d4b_fast_pads.inc"
+#undef FAST_PAD
+
 template <int N, int Nq> struct FL {
+  using P = fast_pad<N, Nq>;
   static constexpr int N2 = N * N, N3 = N * N * N, Q2 = Nq * Nq, Q3 = Nq * Nq * Nq, NQ = N * Nq;
-  /* shared-memory strides chosen so that the 16 lanes of one element (N = 4) hit distinct banks */
-  static constexpr int SJ = N + 1, SK = N * (N + 1), UA = N * SK;        /* U, ACC: (i,j,k) -> i + SJ j + SK k */
-  static constexpr int AS = N2 + (N == 4 ? 4 : 0), AB = Nq * AS;          /* A bufs: (i,j,c) -> i + N j + AS c  */
-  static constexpr int BS = NQ + 1, BB = Nq * BS;                         /* B bufs: (i,b,c) -> i + BS b + N c  */
+  static constexpr int SJ = P::SJ, SK = N * SJ, UA = N * SK;              /* U, ACC: (i,j,k) -> i + SJ j + SK k */
+  static constexpr int AS = P::AS, AB = Nq * AS;                          /* A bufs: (i,j,c) -> i + N j + AS c  */
+  static constexpr int BS = P::BS, BB = Nq * BS;                          /* B bufs: (i,b,c) -> i + BS b + N c  */
   static constexpr int VOL = 2 * AB + 3 * BB;
-  static constexpr int TB = N2 + 1;                                       /* trace block stride */
-  static constexpr int TR = 8 * TB, QV = 4 * 2 * Q2, R1 = 2 * 3 * NQ;
-  static constexpr int S1 = 4 * 3 * NQ, FH = 2 * 4 * Q2, R2 = 2 * 2 * N2;
+  static constexpr int TB = P::TB;                                        /* trace block stride */
+  static constexpr int QP = P::QP;                                        /* stride of a Q2 block of the face scratch */
+  static constexpr int TR = 8 * TB, QV = 4 * 2 * QP, R1 = 2 * 3 * NQ;
+  static constexpr int S1 = 4 * 3 * NQ, FH = 2 * 4 * QP, R2 = 2 * 2 * N2;
   static constexpr int RA = (TR > QV ? (TR > R1 ? TR : R1) : (QV > R1 ? QV : R1));
   static constexpr int RB = (S1 > FH ? (S1 > R2 ? S1 : R2) : (FH > R2 ? FH : R2));
   static constexpr int FACE = RA + RB;
   static constexpr int SCR = VOL > FACE ? VOL : FACE;
-  static constexpr int PER = 2 * UA + SCR;           /* doubles of shared memory per element */
+  static constexpr int PER = 2 * UA + SCR + P::PP;   /* doubles of shared memory per element */
   static constexpr int TPE = N2;                      /* threads per element */
   static constexpr int EPB = (128 / TPE) > 0 ? (128 / TPE) : 1; /* elements per CTA */
   static constexpr int THREADS = TPE * EPB;
@@ -110,7 +123,7 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
 {
   using L = FL<N, Nq>;
   constexpr int N2 = L::N2, N3 = L::N3, Q2 = L::Q2, Q3 = L::Q3, NQ = L::NQ, TPE = L::TPE;
-  constexpr int SJ = L::SJ, SK = L::SK, AS = L::AS, BS = L::BS, TB = L::TB;
+  constexpr int SJ = L::SJ, SK = L::SK, AS = L::AS, BS = L::BS, TB = L::TB, QP = L::QP;
   extern __shared__ double sm[];
   const int le = threadIdx.x / TPE, lt = threadIdx.x % TPE;
   const int slot = blockIdx.x * L::EPB + le;
@@ -278,7 +291,7 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
     }
     __syncthreads();
     /* QV: contraction along face axis b, then fold the gradient with the face factors:
-     * RA[(side*2 + 0)*Q2 + q] = u,  RA[(side*2 + 1)*Q2 + q] = sum_l a_l du/dr_l  (q in MY point order) */
+     * RA[(side*2 + 0)*QP + q] = u,  RA[(side*2 + 1)*QP + q] = sum_l a_l du/dr_l  (q in MY point order) */
     if (active) {
       for (int t = lt; t < 4 * Nq; t += TPE) {
         int qa = t % Nq, side = t / Nq, s = side & 1;
@@ -290,14 +303,14 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
         ld<N>(in, Nq, x); mat1<N, Nq, false>(B, x, u); mat1<N, Nq, false>(C, x, ub);
         ld<N>(in + NQ, Nq, x); mat1<N, Nq, false>(B, x, ua);
         ld<N>(in + 2 * NQ, Nq, x); mat1<N, Nq, false>(B, x, un);
-        double *o = RA + side * 2 * Q2;
+        double *o = RA + side * 2 * QP;
         if (side < 2) {
           const int ia = d == 0 ? 1 : 0, ib = d == 2 ? 1 : 2;
 #pragma unroll
           for (int qb = 0; qb < Nq; qb++) {
             int q = qa + Nq * qb;
             o[q] = u[qb];
-            o[Q2 + q] = F[ia * Q2 + q] * ua[qb] + F[ib * Q2 + q] * ub[qb] + F[d * Q2 + q] * un[qb];
+            o[QP + q] = F[ia * Q2 + q] * ua[qb] + F[ib * Q2 + q] * ub[qb] + F[d * Q2 + q] * un[qb];
           }
         } else {
           const int hc = __ldg(&h->code);
@@ -308,14 +321,14 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
             int xx = (tc & 2) ? Nq - 1 - qa : qa, yy = (tc & 4) ? Nq - 1 - qb : qb;
             int q = (tc & 1) ? xx + Nq * yy : yy + Nq * xx;
             o[q] = u[qb];
-            o[Q2 + q] = F[(3 + ia) * Q2 + q] * ua[qb] + F[(3 + ib) * Q2 + q] * ub[qb] + F[(3 + dp) * Q2 + q] * un[qb];
+            o[QP + q] = F[(3 + ia) * Q2 + q] * ua[qb] + F[(3 + ib) * Q2 + q] * ub[qb] + F[(3 + dp) * Q2 + q] * un[qb];
           }
         }
       }
     }
     __syncthreads();
     /* FLUX at mortar quadrature points (…_flux_sipg.c:645-677 interior, :139-191 Dirichlet):
-     * RB[(face*4 + {F,Ha,Hb,Hn})*Q2 + q] */
+     * RB[(face*4 + {F,Ha,Hb,Hn})*QP + q] */
     if (active) {
       for (int t = lt; t < 2 * Q2; t += TPE) {
         int s = t / Q2, q = t % Q2, qa = q % Nq, qb = q / Nq;
@@ -324,21 +337,21 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
         const bool bnd = s ? nbnd1 : nbnd0;
         double am0 = F[q], am1 = F[Q2 + q], am2 = F[2 * Q2 + q], sjs = F[(bnd ? 3 : 6) * Q2 + q];
         double w = c_ft.w[qa] * c_ft.w[qb];
-        double um = RA[s * 2 * Q2 + q], qm = RA[(s * 2 + 1) * Q2 + q];
+        double um = RA[s * 2 * QP + q], qm = RA[(s * 2 + 1) * QP + q];
         double jump, t1, hs;
         if (!bnd) {
-          jump = um - RA[(4 + 2 * s) * Q2 + q]; t1 = -0.5 * (qm + RA[(5 + 2 * s) * Q2 + q]); hs = -0.5;
+          jump = um - RA[(4 + 2 * s) * QP + q]; t1 = -0.5 * (qm + RA[(5 + 2 * s) * QP + q]); hs = -0.5;
         } else {
           const int64_t go = __ldg(&h->g_off);
           double g = (go >= 0) ? A.bc_g[go + q] : 0.;
           jump = um - g; t1 = -qm; hs = -1.0;
         }
-        double *fh = RB + s * 4 * Q2 + q;
+        double *fh = RB + s * 4 * QP + q;
         double wj = w * hs * jump;
         fh[0] = w * (t1 + sjs * jump);
-        fh[Q2] = wj * (d == 0 ? am1 : am0);
-        fh[2 * Q2] = wj * (d == 2 ? am1 : am2);
-        fh[3 * Q2] = wj * (d == 0 ? am0 : (d == 1 ? am1 : am2));
+        fh[QP] = wj * (d == 0 ? am1 : am0);
+        fh[2 * QP] = wj * (d == 2 ? am1 : am2);
+        fh[3 * QP] = wj * (d == 0 ? am0 : (d == 1 ? am1 : am2));
       }
     }
     __syncthreads();
@@ -346,13 +359,13 @@ d4b_apply_fast_kernel(const fast_args A, const int32_t *__restrict__ frec)
     if (active) {
       for (int t = lt; t < 6 * Nq; t += TPE) {
         int qa = t % Nq, k = (t / Nq) % 3, s = t / (3 * Nq);
-        const double *fh = RB + s * 4 * Q2 + qa;
+        const double *fh = RB + s * 4 * QP + qa;
         double x[Nq], y[N];
         if (k == 0) {
           ld<Nq>(fh, Nq, x); mat1<Nq, N, true>(B, x, y);
-          ld<Nq>(fh + 2 * Q2, Nq, x); mat1_acc<Nq, N, true>(C, x, y);
+          ld<Nq>(fh + 2 * QP, Nq, x); mat1_acc<Nq, N, true>(C, x, y);
         } else {
-          ld<Nq>(fh + (k == 1 ? 1 : 3) * Q2, Nq, x); mat1<Nq, N, true>(B, x, y);
+          ld<Nq>(fh + (k == 1 ? 1 : 3) * QP, Nq, x); mat1<Nq, N, true>(B, x, y);
         }
         st<N>(RA + (s * 3 + k) * NQ + qa, Nq, y);
       }
@@ -480,15 +493,21 @@ static int launch_fast_bucket(const d4b_mesh *m, const d4b_fast_bucket &b, const
  * fork from the caller's stream to the level's side streams, largest bucket first, join back.  A random-hp
  * level has 8-12 launches of very different size; run back to back the small ones cost a launch latency each
  * and the tail of every large one leaves SMs idle. */
-int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st, int *handled)
+/* phase 0: the whole level.  A distributed apply that overlaps its halo exchange (d4b_apply_dev) calls phase 1
+ * -- the batches of the regular buckets that touch no ghost element, while the exchange is in flight -- and
+ * phase 2: the remaining batches, the hp buckets and the completeness kernel, queued behind the exchange. */
+int d4b_launch_phase(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st, int phase)
 {
-  *handled = 1;
   struct item { int kind, idx; double w; };
   item it[2 * D4B_MAX_BUCKETS + 1];
   int n = 0;
-  for (int i = 0; i < m->n_fast; i++) it[n++] = {0, i, (double)m->fast[i].count * m->fast[i].Nq * m->fast[i].Nq * m->fast[i].Nq};
-  for (int i = 0; i < m->n_hp; i++) it[n++] = {1, i, 4.0 * m->hp[i].n_rec / 6.0 * m->hp[i].Nq * m->hp[i].Nq * m->hp[i].Nq};
-  if (m->n_generic > 0) it[n++] = {2, 0, 40.0 * m->n_generic * 64};
+  const d4b_fast_bucket *fb = phase == 0 ? m->fast : (phase == 1 ? m->fast_early : m->fast_late);
+  for (int i = 0; i < m->n_fast; i++)
+    if (fb[i].count > 0) it[n++] = {0, i, (double)fb[i].count * fb[i].Nq * fb[i].Nq * fb[i].Nq};
+  if (phase != 1) {
+    for (int i = 0; i < m->n_hp; i++) it[n++] = {1, i, 4.0 * m->hp[i].n_rec / 6.0 * m->hp[i].Nq * m->hp[i].Nq * m->hp[i].Nq};
+    if (m->n_generic > 0) it[n++] = {2, 0, 40.0 * m->n_generic * 64};
+  }
   for (int i = 1; i < n; i++) { item x = it[i]; int j = i; while (j > 0 && it[j - 1].w < x.w) { it[j] = it[j - 1]; j--; } it[j] = x; }
   static const bool serial = getenv("D4B_NO_CONCURRENT") != nullptr;
   const bool fork = n > 1 && !serial && m->ev_fork;
@@ -502,7 +521,7 @@ int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t
       if (k >= used) { D4B_CUDA(cudaStreamWaitEvent(s, m->ev_fork, 0)); used = k + 1; }
     }
     int rc;
-    if (it[i].kind == 0) rc = launch_fast_bucket(m, m->fast[it[i].idx], u, Au, s);
+    if (it[i].kind == 0) rc = launch_fast_bucket(m, fb[it[i].idx], u, Au, s);
     else if (it[i].kind == 1) rc = d4b_launch_hp_bucket(m, it[i].idx, u, Au, s);
     else rc = d4b_launch_generic(m, u, Au, m->generic_list, m->n_generic, s);
     if (rc != D4B_OK) return rc;
@@ -512,4 +531,10 @@ int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t
     D4B_CUDA(cudaStreamWaitEvent(st, m->ev_join[k], 0));
   }
   return D4B_OK;
+}
+
+int d4b_launch_fast(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st, int *handled)
+{
+  *handled = 1;
+  return d4b_launch_phase(m, u, Au, st, 0);
 }

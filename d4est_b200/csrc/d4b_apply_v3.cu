@@ -1084,6 +1084,56 @@ int d4b_v3_build_late(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges,
   return D4B_OK;
 }
 
+/* bucket made of the slots `list` of b (host list, kept in its order) */
+static int v3_subset(const d4b_fast_bucket &b, const std::vector<int32_t> &list, d4b_fast_bucket *o, cudaStream_t st)
+{
+  o->N = b.N; o->Nq = b.Nq; o->count = 0;
+  o->elem_list = o->frec = o->nrec = nullptr; o->v3_slots = nullptr;
+  const int n = (int)list.size();
+  if (!n) return D4B_OK;
+  int32_t *dl = nullptr;
+  D4B_CUDA(cudaMalloc((void **)&dl, (size_t)n * sizeof(int32_t)));
+  D4B_CUDA(cudaMemcpyAsync(dl, list.data(), (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  D4B_CUDA(cudaMalloc((void **)&o->elem_list, (size_t)n * sizeof(int32_t)));
+  D4B_CUDA(cudaMalloc((void **)&o->frec, (size_t)n * 6 * sizeof(int32_t)));
+  D4B_CUDA(cudaMalloc((void **)&o->nrec, (size_t)n * 6 * sizeof(int32_t)));
+  v3_gather_late<<<(n + 255) / 256, 256, 0, st>>>(n, dl, b.elem_list, b.frec, b.nrec, o->elem_list, o->frec, o->nrec);
+  D4B_CUDA(cudaGetLastError());
+  D4B_CUDA(cudaStreamSynchronize(st));
+  cudaFree(dl);
+  o->count = n;
+  return D4B_OK;
+}
+
+/* For the halo / compute overlap of a distributed apply: split b into the slots whose aligned group of `group`
+ * slots (the warp batch of the kernel that will run them, so the batches -- Morton families -- stay intact and
+ * keep their internal faces) touches no ghost element, and the rest. */
+int d4b_v3_split_ghost(const d4b_mesh *m, const d4b_fast_bucket &b, int group, d4b_fast_bucket *early,
+                       d4b_fast_bucket *late, cudaStream_t st)
+{
+  int rc = v3_prepare_slots(m, b, st);
+  if (rc != D4B_OK) return rc;
+  int32_t *flag = nullptr;
+  D4B_CUDA(cudaMalloc((void **)&flag, (size_t)b.count * sizeof(int32_t)));
+  const int one[2] = {0, b.count};
+  v3_mark_late<<<(b.count + 255) / 256, 256, 0, st>>>((const v3_slot *)b.v3_slots, b.count, v3_make_bounds(1, one),
+                                                      (int64_t)b.N * b.N * b.N, 1 << 30, flag);
+  D4B_CUDA(cudaGetLastError());
+  std::vector<int32_t> h(b.count), le, ll;
+  D4B_CUDA(cudaMemcpyAsync(h.data(), flag, (size_t)b.count * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  D4B_CUDA(cudaStreamSynchronize(st));
+  cudaFree(flag);
+  if (group < 1) group = 1;
+  for (int g0 = 0; g0 < b.count; g0 += group) {
+    const int g1 = g0 + group < b.count ? g0 + group : b.count;
+    bool any = false;
+    for (int s = g0; s < g1; s++) any = any || h[s];
+    for (int s = g0; s < g1; s++) (any ? ll : le).push_back(s);
+  }
+  if ((rc = v3_subset(b, le, early, st)) != D4B_OK) return rc;
+  return v3_subset(b, ll, late, st);
+}
+
 template <int N, int Nq>
 static int v3_launch_t(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st,
                        int slot_begin, int slot_end)

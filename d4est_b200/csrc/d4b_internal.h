@@ -64,6 +64,11 @@ struct d4b_mesh {
   #define D4B_NSIDE 6
   cudaStream_t side[D4B_NSIDE]; cudaEvent_t ev_fork, ev_join[D4B_NSIDE];   /* concurrent bucket launches of one apply */
   int32_t *generic_list; int n_generic;   /* elements left to the generic kernel */
+  /* halo / compute overlap of a distributed apply (d4b_apply_dev): every regular bucket is split once into the
+   * batches that touch no ghost element (launched while the exchange runs on comm_stream) and the rest */
+  int split_built;                 /* 0 not yet, 1 built, -1 nothing to overlap (no ghost-free regular batch) */
+  d4b_fast_bucket fast_early[D4B_MAX_BUCKETS], fast_late[D4B_MAX_BUCKETS];
+  cudaStream_t comm_stream; cudaEvent_t ev_cfork, ev_halo;
 };
 
 /* Per-slot metadata, resolved once per bucket (v3_build_slots): one coalesced read per element
@@ -96,6 +101,7 @@ int d4b_launch_v3_range(const d4b_mesh *m, const d4b_fast_bucket &b, const doubl
                         int slot_begin, int slot_end);
 int d4b_v3_elems_per_cta(int N, int Nq);
 int d4b_v3_build_late(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, const int *bounds, int lookahead, d4b_fast_bucket *late, cudaStream_t st);
+int d4b_v3_split_ghost(const d4b_mesh *m, const d4b_fast_bucket &b, int group, d4b_fast_bucket *early, d4b_fast_bucket *late, cudaStream_t st);
 int d4b_v3_range_need(const d4b_mesh *m, const d4b_fast_bucket &b, int n_ranges, const int *bounds, int *need_host, cudaStream_t st);
 /* split elements into fast buckets + generic list; D->hm == NULL means the uniform device-built brick */
 int d4b_fast_classify(d4b_mesh *m, const d4b_mesh_desc_t *D);
