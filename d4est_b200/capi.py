@@ -79,6 +79,7 @@ SYMBOLS = {
     "d4b_vec_copy": (C.c_int, [C.c_int64, _P, _P, _P]),
     "d4b_vec_zero": (C.c_int, [C.c_int64, _P, _P]),
     "d4b_vec_dot": (C.c_int, [C.c_int64, _P, _P, C.POINTER(C.c_double), _P]),
+    "d4b_vec_dot_noalloc": (C.c_int, [C.c_int64, _P, _P, _P, _P]),
     "d4b_cheby_iterate": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_double, C.c_double, C.c_int, _P, _P]),
     "d4b_cg_eigs": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.POINTER(C.c_double), _P, _P]),
     "d4b_cg_solve": (C.c_int, [_P, _P, _P, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_double), _P, _P]),

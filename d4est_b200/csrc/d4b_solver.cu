@@ -300,6 +300,47 @@ int d4b_vec_dot(int64_t n, const double *x, const double *y, double *result, voi
   return D4B_OK;
 }
 
+/* ---- allocation-free dot product ---------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same two kernels as d4b_vec_dot
+ * (k_dots_partial + k_dots_final, same grid, so the same bits), but the block partials live in a file-scope device
+ * array instead of cudaMalloc'ed scratch and the result is written to a caller-supplied DEVICE double.  The array
+ * is 4 * VGRID_MAX doubles = 75 776 bytes and stays resident on every GPU that loads the library.  In host code
+ * `g_noalloc_part` is only the host-side stand-in of the symbol: the device address comes from
+ * cudaGetSymbolAddress, once per device, with that device current.  Every call shares the array: calls that
+ * overlap on the GPU (different streams) race on it; calls on one stream are ordered.  Nothing in it has to start
+ * at zero -- the first kernel overwrites every partial the second one reads. */
+#define D4B_NOALLOC_MAX_DEV 64
+static __device__ __align__(256) double g_noalloc_part[4 * VGRID_MAX];
+static double *g_noalloc_ptr[D4B_NOALLOC_MAX_DEV];
+
+int d4b_vec_dot_noalloc(int64_t n, const double *x, const double *y, double *result_dev, void *stream)
+{
+  if (n < 0 || n > D4B_NOALLOC_DOT_MAX_N) {
+    d4b_set_error("d4b_vec_dot_noalloc: n = %lld is outside [0, %lld] (D4B_NOALLOC_DOT_MAX_N)", (long long)n,
+                  (long long)D4B_NOALLOC_DOT_MAX_N);
+    return D4B_EINVAL;
+  }
+  if (!result_dev || (n > 0 && (!x || !y))) { d4b_set_error("d4b_vec_dot_noalloc: NULL vector or result pointer"); return D4B_EINVAL; }
+  int dev = -1;
+  D4B_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= D4B_NOALLOC_MAX_DEV) { d4b_set_error("d4b_vec_dot_noalloc: device ordinal %d is not supported", dev); return D4B_EINVAL; }
+  if (!g_noalloc_ptr[dev]) {   /* set-up, once per device: resolve the symbol's device address */
+    double *ptr = nullptr;
+    D4B_CUDA(cudaGetSymbolAddress((void **)&ptr, g_noalloc_part));
+    if (!ptr) { d4b_set_error("d4b_vec_dot_noalloc: cudaGetSymbolAddress returned NULL"); return D4B_ECUDA; }
+    g_noalloc_ptr[dev] = ptr;
+  }
+  double *part = g_noalloc_ptr[dev];
+  dot_args a; a.k = 1;
+  for (int j = 0; j < 4; j++) { a.x[j] = x; a.y[j] = y; }
+  const int g = vgrid(n);
+  k_dots_partial<<<g, VB, 0, ST>>>(n, a, part);
+  k_dots_final<<<1, VB, 0, ST>>>(g, 1, part, result_dev);
+  LAUNCH(2);
+  return D4B_OK;
+}
+
 /* Chebyshev semi-iteration with a HOST interval: restates d4est_solver_multigrid_smoother_cheby_iterate_aux
  * (Solver/d4est_solver_multigrid_smoother_cheby.c:81-176).  work: 2 n doubles (Au, p).
  * On return r = rhs - A u (the residual the V-cycle restricts, multigrid.c:1054). */

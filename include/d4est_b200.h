@@ -174,6 +174,16 @@ int d4b_vec_scale(int64_t n, double a, double *x, void *cuda_stream);
 int d4b_vec_copy(int64_t n, const double *x, double *y, void *cuda_stream);
 int d4b_vec_zero(int64_t n, double *x, void *cuda_stream);
 int d4b_vec_dot(int64_t n, const double *x, const double *y, double *result_host, void *cuda_stream);
+/* Allocation-free dot product.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * result_dev[0] = sum_i x[i] y[i] over THIS rank's n entries (no NCCL call: the caller reduces over ranks), written
+ * on the device, in stream order; x, y, result_dev are device pointers.  Calls no cudaMalloc / cudaFree / pinned
+ * allocation: the block partials live in a static device array of 75 776 bytes that every GPU loading the library
+ * holds until exit.  n > D4B_NOALLOC_DOT_MAX_N is rejected with D4B_EINVAL.  All calls share that array: calls that
+ * overlap on the GPU (different streams, no ordering) race; calls on one stream are safe.  The first call on a
+ * device resolves the array's address (cudaGetSymbolAddress); make it outside a graph capture. */
+#define D4B_NOALLOC_DOT_MAX_N ((int64_t)1 << 28)
+int d4b_vec_dot_noalloc(int64_t n, const double *x, const double *y, double *result_dev, void *cuda_stream);
 
 /* ---- Chebyshev smoother + CG spectral bound (device vectors; `work` = caller scratch)
  *      d4est_solver_multigrid_smoother_cheby_iterate_aux  Solver/d4est_solver_multigrid_smoother_cheby.c:81
