@@ -176,7 +176,7 @@ def morton_order(nx, ny, nz):
     return ix[o], iy[o], iz[o]
 
 
-def halo_check(d4est_b200, rank, world, deg, n=12):
+def halo_check(d4est_b200, rank, world, deg, n=32):   # 32^3 per slab: above the overlap threshold, so the overlapped exchange is what is checked
     """Correctness of the NCCL data plane inside the bench: every rank applies the operator to ITS slab of a small
     brick n x n x (n world) through d4b_apply_dev (pack kernel + ncclSend/ncclRecv of the mirror planes + element
     kernel) and compares with the same elements of a whole-brick apply computed on its own GPU without any halo.

@@ -51,8 +51,14 @@ def main():
         dist.broadcast(t, 0)
         idbuf = ctypes.create_string_buffer(bytes(t.cpu().tolist()), 128)
         capi.check(L.d4b_comm_init(rank, world, idbuf))
+        # small fixtures: lift the size threshold so that the apply overlaps its exchange with the ghost-free batches
+        capi.check(L.d4b_set_option(b"overlap_min_elements", 0))
         lvl = d4est_b200.MeshLevel(me)
         Au = lvl.apply_host(ul)          # halo exchange over NCCL inside the apply
+        capi.check(L.d4b_set_option(b"no_overlap", 1))
+        Au_serial = lvl.apply_host(ul)   # exchange-then-apply: same kernels on the same data, same bits
+        capi.check(L.d4b_set_option(b"no_overlap", 0))
+        assert np.array_equal(Au, Au_serial), "overlapped and exchange-then-apply results differ"
         ref = fx["Au_ref_with_opt"][a:b]
         krylov_ok = True
         if len(sys.argv) > 3 and sys.argv[3] == "krylov" and fx["bc_g"].size == 0:
