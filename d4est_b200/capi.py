@@ -89,6 +89,10 @@ SYMBOLS = {
     "d4b_mg_transfer_destroy": (None, [_P]),
     "d4b_mg_restrict": (C.c_int, [_P, _P, _P, _P]),
     "d4b_mg_prolong": (C.c_int, [_P, _P, _P, _P]),
+    "d4b_amr_transfer_create": (C.c_int, [C.c_int, _P, _P, C.POINTER(_P), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "d4b_amr_interpolate_field_sizes": (C.c_int, [C.c_int, _P, _P, C.c_int, _P, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "d4b_amr_interpolate_field_dev": (C.c_int, [C.c_int, _P, _P, C.c_int, _P, _P, _P, _P, _P]),
+    "d4b_amr_interpolate_field_host": (C.c_int, [C.c_int, _P, _P, C.c_int, _P, _P, C.c_int64, _P, C.c_int64]),
     "d4b_mg_create": (C.c_int, [C.c_int, C.POINTER(_P), C.POINTER(_P), _P, C.POINTER(_P)]),
     "d4b_mg_destroy": (None, [_P]),
     "d4b_mg_get_eigs": (C.c_int, [_P, _P]),

@@ -168,6 +168,99 @@ int d4b_mg_restrict(d4b_mg_transfer_t *T, const double *fine, double *coarse, vo
 int d4b_mg_prolong(d4b_mg_transfer_t *T, const double *coarse, double *fine, void *stream)
 { return transfer(T, 1, coarse, fine, (cudaStream_t)stream); }
 
+/* ---- AMR field transfer (second half): d4est_amr_interpolate_field (hpAMR/d4est_amr.c:406-485) carries
+ * a nodal field from the old grid to the new one in two sweeps driven by the logs of d4est_amr_step: initial grid ->
+ * refined grid (element i of degree initial_log[i]: refinement_log[i] = -deg -> 8 children of the same degree by
+ * hp-prolongation, = deg' >= deg -> p-prolongation, :338-403) and refined grid -> 2:1-balanced grid (balance_log[i] =
+ * -deg -> 8 children, +deg -> copy).  Both sweeps are the prolongation of a transfer table (k_mg_transfer, one CTA
+ * per old element), elements and children in log order, which is the order of the nodal vectors. */
+int d4b_amr_transfer_create(int n, const int32_t *deg_in, const int32_t *code, d4b_mg_transfer_t **out,
+                            int64_t *nodes_in, int64_t *nodes_out)
+{
+  *out = nullptr;
+  std::vector<int32_t> kind(n), degH(n), cdeg(8 * (size_t)n, 0);
+  std::vector<int64_t> coff(n), choff(8 * (size_t)n, 0);
+  int64_t ni = 0, no = 0;
+  for (int e = 0; e < n; e++) {
+    const int d = deg_in[e] < 0 ? -deg_in[e] : deg_in[e], c = code[e];
+    if (d < 1 || d > D4B_MAX_DEG) { d4b_set_error("amr transfer: element %d has degree %d", e, d); return D4B_EINVAL; }
+    const int64_t nin = (int64_t)(d + 1) * (d + 1) * (d + 1);
+    degH[e] = d; coff[e] = ni; ni += nin;
+    if (c < 0) {   /* h-refinement keeps the degree (the reference asserts it, d4est_amr.c:352) */
+      if (-c != d) { d4b_set_error("amr transfer: element %d: h-refinement code %d with degree %d", e, c, d); return D4B_EINVAL; }
+      kind[e] = 1;
+      for (int k = 0; k < 8; k++) { cdeg[8 * (size_t)e + k] = d; choff[8 * (size_t)e + k] = no; no += nin; }
+    } else {       /* p-refinement; coarsening is not supported by the reference either (it aborts, :395) */
+      if (c < d || c > D4B_MAX_DEG) { d4b_set_error("amr transfer: element %d: code %d with degree %d (coarsening is not supported)", e, c, d); return D4B_EINVAL; }
+      kind[e] = 0; cdeg[8 * (size_t)e] = c; choff[8 * (size_t)e] = no; no += (int64_t)(c + 1) * (c + 1) * (c + 1);
+    }
+  }
+  if (nodes_in) *nodes_in = ni;
+  if (nodes_out) *nodes_out = no;
+  return d4b_mg_transfer_create(n, kind.data(), degH.data(), coff.data(), cdeg.data(), choff.data(), out);
+}
+
+/* field_out (n_out nodes, balanced grid) from field_in (n_in nodes, initial grid); device pointers; aux_dev holds
+ * the refined, not yet balanced field (sum of the first sweep's output sizes, returned by the _sizes call) */
+int d4b_amr_interpolate_field_sizes(int n_init, const int32_t *initial_log, const int32_t *refinement_log, int n_bal,
+                                    const int32_t *balance_log, int64_t *n_in, int64_t *n_aux, int64_t *n_out)
+{
+  int64_t a = 0, b = 0, c = 0;
+  for (int i = 0; i < n_init; i++) {
+    const int d = initial_log[i], r = refinement_log[i], q = r < 0 ? -r : r;
+    a += (int64_t)(d + 1) * (d + 1) * (d + 1);
+    b += (int64_t)(q + 1) * (q + 1) * (q + 1) * (r < 0 ? 8 : 1);
+  }
+  int64_t b2 = 0;
+  for (int i = 0; i < n_bal; i++) {
+    const int r = balance_log[i], q = r < 0 ? -r : r;
+    b2 += (int64_t)(q + 1) * (q + 1) * (q + 1);
+    c += (int64_t)(q + 1) * (q + 1) * (q + 1) * (r < 0 ? 8 : 1);
+  }
+  if (b != b2) { d4b_set_error("amr transfer: the refinement log produces %lld nodes, the balance log consumes %lld", (long long)b, (long long)b2); return D4B_EINVAL; }
+  if (n_in) *n_in = a;
+  if (n_aux) *n_aux = b;
+  if (n_out) *n_out = c;
+  return D4B_OK;
+}
+int d4b_amr_interpolate_field_dev(int n_init, const int32_t *initial_log, const int32_t *refinement_log, int n_bal,
+                                  const int32_t *balance_log, const double *in_dev, double *aux_dev, double *out_dev,
+                                  void *stream)
+{
+  int rc;
+  if ((rc = d4b_amr_interpolate_field_sizes(n_init, initial_log, refinement_log, n_bal, balance_log, nullptr, nullptr, nullptr))) return rc;
+  d4b_mg_transfer_t *T1 = nullptr, *T2 = nullptr;
+  if ((rc = d4b_amr_transfer_create(n_init, initial_log, refinement_log, &T1, nullptr, nullptr))) return rc;
+  if ((rc = d4b_amr_transfer_create(n_bal, balance_log, balance_log, &T2, nullptr, nullptr))) { d4b_mg_transfer_destroy(T1); return rc; }
+  rc = d4b_mg_prolong(T1, in_dev, aux_dev, stream);
+  if (!rc) rc = d4b_mg_prolong(T2, aux_dev, out_dev, stream);
+  cudaError_t ce = cudaStreamSynchronize((cudaStream_t)stream);   /* the tables are freed below */
+  d4b_mg_transfer_destroy(T1); d4b_mg_transfer_destroy(T2);
+  if (!rc && ce != cudaSuccess) { d4b_set_error("amr transfer: %s", cudaGetErrorString(ce)); rc = D4B_ECUDA; }
+  return rc;
+}
+int d4b_amr_interpolate_field_host(int n_init, const int32_t *initial_log, const int32_t *refinement_log, int n_bal,
+                                   const int32_t *balance_log, const double *field_in, int64_t n_in, double *field_out,
+                                   int64_t n_out)
+{
+  int64_t a, b, c; int rc;
+  if ((rc = d4b_amr_interpolate_field_sizes(n_init, initial_log, refinement_log, n_bal, balance_log, &a, &b, &c))) return rc;
+  if (a != n_in || c != n_out) {
+    d4b_set_error("amr transfer: the logs describe %lld -> %lld nodes, the caller passed %lld -> %lld", (long long)a, (long long)c, (long long)n_in, (long long)n_out);
+    return D4B_EINVAL;
+  }
+  double *d = nullptr;
+  D4B_CUDA(cudaMalloc((void **)&d, (size_t)(a + b + c + 1) * sizeof(double)));
+  cudaError_t ce = cudaMemcpy(d, field_in, (size_t)a * sizeof(double), cudaMemcpyHostToDevice);
+  if (ce == cudaSuccess) {
+    rc = d4b_amr_interpolate_field_dev(n_init, initial_log, refinement_log, n_bal, balance_log, d, d + a, d + a + b, nullptr);
+    if (!rc) ce = cudaMemcpy(field_out, d + a + b, (size_t)c * sizeof(double), cudaMemcpyDeviceToHost);
+  }
+  cudaFree(d);
+  if (!rc && ce != cudaSuccess) { d4b_set_error("amr transfer: %s", cudaGetErrorString(ce)); rc = D4B_ECUDA; }
+  return rc;
+}
+
 int d4b_mg_create(int n_levels, d4b_mesh_t **levels, d4b_mg_transfer_t **transfers, const d4b_mg_params_t *par,
                   d4b_mg_t **out)
 {

@@ -325,6 +325,27 @@ int d4est_b200_fcg_solve(p4est_t *p4est, d4est_elliptic_data_t *vecs, d4est_elli
 }
 
 /* ------------------------------------------------------------------ PETSc hooks (PETSc is not in this snapshot) */
+/* ---- AMR field transfer: what d4est_amr_interpolate_field (hpAMR/d4est_amr.c:406-485) does with the logs of the
+ * step that has just run, on the GPU.  *field is reallocated the way the reference does it (D4EST_REALLOC there). */
+int d4est_b200_amr_interpolate_field(d4est_amr_t *d4est_amr, double **field, int post_balance_nodes)
+{
+  int64_t n_in = 0, n_aux = 0, n_out = 0;
+  int rc = d4b_amr_interpolate_field_sizes(d4est_amr->initial_log_size, d4est_amr->initial_log, d4est_amr->refinement_log,
+                                           d4est_amr->balance_log_size, d4est_amr->balance_log, &n_in, &n_aux, &n_out);
+  if (rc != D4B_OK) return rc;
+  if (n_out != post_balance_nodes) {
+    fprintf(stderr, "d4est_b200_amr_interpolate_field: logs give %lld nodes, the mesh has %d\n", (long long)n_out, post_balance_nodes);
+    return D4B_EINVAL;
+  }
+  double *out = D4EST_ALLOC(double, post_balance_nodes);
+  rc = d4b_amr_interpolate_field_host(d4est_amr->initial_log_size, d4est_amr->initial_log, d4est_amr->refinement_log,
+                                      d4est_amr->balance_log_size, d4est_amr->balance_log, *field, n_in, out, n_out);
+  if (rc != D4B_OK) { D4EST_FREE(out); return rc; }
+  D4EST_FREE(*field);
+  *field = out;
+  return D4B_OK;
+}
+
 #ifdef D4EST_B200_HAVE_PETSC
 #include <petscsnes.h>
 /* MatShell multiply, installed with MatShellSetOperation(A, MATOP_MULT, ...) in place of

@@ -226,6 +226,24 @@ int d4b_mg_transfer_create(int n_coarse, const int32_t *kind, const int32_t *deg
 void d4b_mg_transfer_destroy(d4b_mg_transfer_t *T);
 int d4b_mg_restrict(d4b_mg_transfer_t *T, const double *fine_dev, double *coarse_dev, void *cuda_stream);
 int d4b_mg_prolong(d4b_mg_transfer_t *T, const double *coarse_dev, double *fine_dev, void *cuda_stream);
+/* ---- AMR field transfer (old grid -> refined grid -> 2:1-balanced grid), driven by the logs of d4est_amr_step:
+ *      d4est_amr_interpolate_field              hpAMR/d4est_amr.c:406-485
+ *      d4est_amr_interpolate_field_on_element   hpAMR/d4est_amr.c:338-403 (code < 0: 8 children of the same degree by
+ *                                               hp-prolongation; code >= deg: p-prolongation; coarsening aborts there,
+ *                                               D4B_EINVAL here)
+ *      d4b_amr_transfer_create builds the transfer table of ONE sweep (element i of degree |deg_in[i]| with code[i]);
+ *      apply it with d4b_mg_prolong.  The _dev form runs both sweeps on device vectors (aux_dev: n_aux doubles from
+ *      _sizes); the _host form stages host vectors (the call the glue makes for d4est's double** field). */
+int d4b_amr_transfer_create(int n, const int32_t *deg_in, const int32_t *code, d4b_mg_transfer_t **out,
+                            int64_t *nodes_in, int64_t *nodes_out);
+int d4b_amr_interpolate_field_sizes(int n_init, const int32_t *initial_log, const int32_t *refinement_log, int n_bal,
+                                    const int32_t *balance_log, int64_t *n_in, int64_t *n_aux, int64_t *n_out);
+int d4b_amr_interpolate_field_dev(int n_init, const int32_t *initial_log, const int32_t *refinement_log, int n_bal,
+                                  const int32_t *balance_log, const double *in_dev, double *aux_dev, double *out_dev,
+                                  void *cuda_stream);
+int d4b_amr_interpolate_field_host(int n_init, const int32_t *initial_log, const int32_t *refinement_log, int n_bal,
+                                   const int32_t *balance_log, const double *field_in, int64_t n_in, double *field_out,
+                                   int64_t n_out);
 /* levels[0] = coarsest ... levels[n-1] = finest; transfers[l] joins l (coarse) and l+1 (fine) */
 int d4b_mg_create(int n_levels, d4b_mesh_t **levels, d4b_mg_transfer_t **transfers, const d4b_mg_params_t *par,
                   d4b_mg_t **out);

@@ -23,6 +23,7 @@
 #include <d4est_quadrature.h>
 #include <d4est_mesh.h>
 #include <d4est_laplacian_with_opt_flux.h>
+#include <d4est_amr.h>
 #include "d4est_b200.h"
 
 /* Flatten one mesh level into the pointer-and-size description.  All arrays in the
@@ -134,6 +135,12 @@ int d4est_b200_fcg_solve(p4est_t *p4est, d4est_elliptic_data_t *vecs, d4est_elli
                          d4est_ghost_t **ghost, d4est_ghost_data_t **ghost_data, d4est_operators_t *ops,
                          d4est_geometry_t *geom, d4est_quadrature_t *quad, d4est_mesh_data_t *factors, void *fcg_params,
                          d4est_krylov_pc_t *pc, int amr_level, int newton_iteration);
+
+/* (4b) AMR field transfer: same effect as the static d4est_amr_interpolate_field(p4est, ops, d4est_amr, field,
+ *      post_balance_nodes) (hpAMR/d4est_amr.c:406, called from d4est_amr_step :1052) -- *field is replaced by the
+ *      field on the refined and balanced grid, computed on the GPU from the logs d4est_amr_step has just filled.
+ *      Returns 0 or a D4B_E* code (d4b_last_error()). */
+int d4est_b200_amr_interpolate_field(d4est_amr_t *d4est_amr, double **field, int post_balance_nodes);
 
 /* (5) with -DD4EST_B200_HAVE_PETSC: PetscErrorCode d4est_b200_krylov_petsc_apply_aij(Mat, Vec, Vec), the MatShell
  *     multiply (Solver/d4est_solver_krylov_petsc.c:273, installed :428). */

@@ -141,6 +141,38 @@ def transfer(tab, src, n_dst, restrict):
     return dst
 
 
+def amr_sweep_table(deg_in, code):
+    """Transfer table of one sweep of d4est_amr_interpolate_field (hpAMR/d4est_amr.c:406-485): element i of degree
+    |deg_in[i]| with code[i] < 0 -> 8 children of the same degree (hp-prolongation, :366), code[i] >= deg ->
+    p-prolongation (:379); coarsening aborts in the reference (:395)."""
+    n = len(deg_in)
+    tab = {"kind": np.zeros(n, np.int32), "degH": np.zeros(n, np.int32), "coarse_off": np.zeros(n, np.int64),
+           "child_deg": np.zeros(8 * n, np.int32), "child_off": np.zeros(8 * n, np.int64)}
+    ni = no = 0
+    for e in range(n):
+        d, c = abs(int(deg_in[e])), int(code[e])
+        tab["degH"][e] = d; tab["coarse_off"][e] = ni; ni += (d + 1) ** 3
+        if c < 0:
+            assert -c == d, "h-refinement keeps the degree"
+            tab["kind"][e] = 1
+            for k in range(8):
+                tab["child_deg"][8 * e + k] = d; tab["child_off"][8 * e + k] = no; no += (d + 1) ** 3
+        else:
+            assert c >= d, "coarsening is not supported"
+            tab["child_deg"][8 * e] = c; tab["child_off"][8 * e] = no; no += (c + 1) ** 3
+    return tab, ni, no
+
+
+def amr_interpolate_field(initial_log, refinement_log, balance_log, field):
+    """d4est_amr_interpolate_field: initial grid -> refined grid -> 2:1-balanced grid."""
+    t1, n_in, n_aux = amr_sweep_table(initial_log, refinement_log)
+    assert n_in == field.size
+    aux = transfer(t1, field, n_aux, restrict=False)
+    t2, n_aux2, n_out = amr_sweep_table(balance_log, balance_log)
+    assert n_aux2 == n_aux
+    return transfer(t2, aux, n_out, restrict=False)
+
+
 def brick_transfer_table(n_coarse_per_dir, deg):
     """Transfer table between Morton-ordered uniform bricks 2n -> n with equal degree: the 8 children
     of coarse element e are fine elements 8e .. 8e+7 (child c = bits r,s,t = Morton order)."""

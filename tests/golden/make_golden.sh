@@ -8,3 +8,4 @@ cd "$(dirname "$0")/../.."
 H=oracle/_ref/d4b_harness
 $H oracle/inputs/brick_p3_l2.input none 0 zero sinrand tests/golden/brick_p3_l2.fix
 $H oracle/inputs/cubed_sphere_hp.input random_hp 1 poly polyrand tests/golden/cubed_sphere_hp1.fix
+oracle/_ref/d4b_amr_harness oracle/inputs/cubed_sphere_hp.input 2 tests/golden/amr_transfer_cubed_sphere_hp2.fix

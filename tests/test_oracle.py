@@ -182,3 +182,24 @@ def test_mass_term_oracle_matches_reference(ref_fixture_dir):
     if "mass_ref" not in fx:
         pytest.skip("fixture predates the mass-term reference")
     assert rel(dg_oracle.mass_apply(fx, fx["mass_coef"], fx["u"]), fx["mass_ref"]) < TOL
+
+
+def test_amr_field_transfer_oracle_matches_reference(golden_dir):
+    """d4est_amr_step with a field attached (unmodified reference, oracle/harness/d4b_amr_harness.c): the numpy
+    restatement of d4est_amr_interpolate_field reproduces the reference's field after every step."""
+    import solver_oracle as so
+    fx = fixture.load(os.path.join(golden_dir, "amr_transfer_cubed_sphere_hp2.fix"))
+    steps = int(fx["steps"][0])
+    assert steps == 2
+    kinds = set()
+    for k in range(steps):
+        il, rl, bl = fx[f"S{k}.initial_log"], fx[f"S{k}.refinement_log"], fx[f"S{k}.balance_log"]
+        kinds |= {("h" if c < 0 else ("p" if c > d else "keep")) for d, c in zip(il, rl)}
+        kinds |= {"balance_h"} if (bl < 0).any() else set()
+        out = so.amr_interpolate_field(il, rl, bl, fx[f"S{k}.field_pre"])
+        ref = fx[f"S{k}.field_post"]
+        assert out.shape == ref.shape
+        assert np.abs(out - ref).max() <= 1e-13 * np.abs(ref).max()
+        if k + 1 < steps:   # the reference chains the steps: its output is the next step's input, bit for bit
+            assert np.array_equal(ref, fx[f"S{k + 1}.field_pre"])
+    assert {"h", "p", "balance_h"} <= kinds   # the fixture exercises h-, p-refinement and the 2:1 balance sweep
