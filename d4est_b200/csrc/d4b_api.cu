@@ -24,7 +24,7 @@ int d4b_launch_phase(const d4b_mesh *m, const double *u, double *Au, cudaStream_
 int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_t> &cand, std::vector<int32_t> &rest);
 
 /* run-time switches of the host pipeline: defaults from the environment (read ONCE), changed by d4b_set_option */
-static struct { bool init; int no_late_pass, no_pipeline, pipe_trace, pipe_chunks, no_overlap, overlap_min; } g_opt;
+static struct { bool init; int no_late_pass, no_pipeline, pipe_trace, pipe_chunks, no_overlap, overlap_min, tp_min; } g_opt;
 static void opts_init()
 {
   if (g_opt.init) return;
@@ -33,9 +33,11 @@ static void opts_init()
   g_opt.pipe_chunks = getenv("D4B_PIPE_CHUNKS") ? atoi(getenv("D4B_PIPE_CHUNKS")) : 0;
   g_opt.no_overlap = getenv("D4B_NO_OVERLAP") != nullptr;
   g_opt.overlap_min = getenv("D4B_OVERLAP_MIN") ? atoi(getenv("D4B_OVERLAP_MIN")) : 16384;
+  g_opt.tp_min = getenv("D4B_NO_TP") ? 0x7fffffff : (getenv("D4B_TP_MIN") ? atoi(getenv("D4B_TP_MIN")) : 4096);
   g_opt.init = true;
 }
 extern int g_fcg_textbook;   /* d4b_solver.cu */
+int d4b_opt_tp_min() { opts_init(); return g_opt.tp_min; }   /* d4b_apply_hp.cu */
 
 extern "C" {
 
@@ -49,6 +51,7 @@ int d4b_set_option(const char *name, int value)
   else if (!strcmp(name, "pipe_trace")) g_opt.pipe_trace = value;
   else if (!strcmp(name, "pipe_chunks")) g_opt.pipe_chunks = value;
   else if (!strcmp(name, "no_overlap")) g_opt.no_overlap = value;
+  else if (!strcmp(name, "two_pass_min_elements")) g_opt.tp_min = value;         /* read when a level is created */
   else if (!strcmp(name, "overlap_min_elements")) g_opt.overlap_min = value;   /* read when a level first exchanges */
   else { d4b_set_error("unknown option %s", name); return D4B_EINVAL; }
   return D4B_OK;
@@ -253,6 +256,9 @@ void d4b_mesh_destroy(d4b_mesh_t *m)
   cudaFree(m->u_stage); cudaFree(m->Au_stage); cudaFree(m->host_work); cudaFree(m->sc); cudaFree(m->dot_part); if (m->sc_h) cudaFreeHost(m->sc_h); cudaFree(m->send_elem); cudaFree(m->send_buf); cudaFree(m->send_off);
   for (int i = 0; i < m->n_fast; i++) { cudaFree(m->fast[i].elem_list); cudaFree(m->fast[i].frec); cudaFree(m->fast[i].nrec); cudaFree(m->fast[i].v3_slots); }
   for (int i = 0; i < m->n_hp; i++) { cudaFree(m->hp[i].slots); cudaFree(m->hp[i].recs); }
+  for (int i = 0; i < m->n_tp1; i++) { cudaFree(m->tp1[i].slots); cudaFree(m->tp1[i].recs); }
+  for (int i = 0; i < m->n_tp2; i++) { cudaFree(m->tp2[i].slots); cudaFree(m->tp2[i].recs); }
+  cudaFree(m->tpW);
   cudaFree(m->generic_list);
   free(m->peer_rank_h); free(m->send_begin_h); free(m->recv_begin_h);
   free(m->send_node_begin_h); free(m->recv_node_begin_h);
@@ -280,6 +286,7 @@ int d4b_mesh_kernel_split(const d4b_mesh_t *m, int64_t counts[3])
   counts[0] = counts[1] = 0; counts[2] = m->n_generic;
   for (int i = 0; i < m->n_fast; i++) counts[0] += m->fast[i].count;
   for (int i = 0; i < m->n_hp; i++) counts[1] += m->hp[i].count;
+  for (int i = 0; i < m->n_tp2; i++) counts[1] += m->tp2[i].count;   /* two-pass hp elements */
   return D4B_OK;
 }
 

@@ -499,36 +499,49 @@ static int launch_fast_bucket(const d4b_mesh *m, const d4b_fast_bucket &b, const
 int d4b_launch_phase(const d4b_mesh *m, const double *u, double *Au, cudaStream_t st, int phase)
 {
   struct item { int kind, idx; double w; };
-  item it[2 * D4B_MAX_BUCKETS + 1];
-  int n = 0;
-  const d4b_fast_bucket *fb = phase == 0 ? m->fast : (phase == 1 ? m->fast_early : m->fast_late);
-  for (int i = 0; i < m->n_fast; i++)
-    if (fb[i].count > 0) it[n++] = {0, i, (double)fb[i].count * fb[i].Nq * fb[i].Nq * fb[i].Nq};
-  if (phase != 1) {
-    for (int i = 0; i < m->n_hp; i++) it[n++] = {1, i, 4.0 * m->hp[i].n_rec / 6.0 * m->hp[i].Nq * m->hp[i].Nq * m->hp[i].Nq};
-    if (m->n_generic > 0) it[n++] = {2, 0, 40.0 * m->n_generic * 64};
-  }
-  for (int i = 1; i < n; i++) { item x = it[i]; int j = i; while (j > 0 && it[j - 1].w < x.w) { it[j] = it[j - 1]; j--; } it[j] = x; }
   static const bool serial = getenv("D4B_NO_CONCURRENT") != nullptr;
-  const bool fork = n > 1 && !serial && m->ev_fork;
-  int used = 0;
-  if (fork) D4B_CUDA(cudaEventRecord(m->ev_fork, st));
-  for (int i = 0; i < n; i++) {
-    cudaStream_t s = st;
-    if (fork && i > 0) {
-      const int k = (i - 1) % D4B_NSIDE;
-      s = m->side[k];
-      if (k >= used) { D4B_CUDA(cudaStreamWaitEvent(s, m->ev_fork, 0)); used = k + 1; }
+  const d4b_fast_bucket *fb = phase == 0 ? m->fast : (phase == 1 ? m->fast_early : m->fast_late);
+  /* round 0: everything but pass 2 of the two-pass hp path; round 1: pass 2 (it reads the traces W that ALL pass-1
+   * launches of round 0 write, so it starts after the join of round 0) */
+  for (int round = 0; round < 2; round++) {
+    item it[4 * D4B_MAX_BUCKETS + 1];
+    int n = 0;
+    if (round == 0) {
+      for (int i = 0; i < m->n_fast; i++)
+        if (fb[i].count > 0) it[n++] = {0, i, (double)fb[i].count * fb[i].Nq * fb[i].Nq * fb[i].Nq};
+      if (phase != 1) {
+        for (int i = 0; i < m->n_hp; i++) it[n++] = {1, i, 4.0 * m->hp[i].n_rec / 6.0 * m->hp[i].Nq * m->hp[i].Nq * m->hp[i].Nq};
+        if (m->n_generic > 0) it[n++] = {2, 0, 40.0 * m->n_generic * 64};
+        /* the trace launches first: round 1 waits for them */
+        for (int i = 0; i < m->n_tp1; i++) it[n++] = {3, i, 1e15 + 2.0 * m->tp1[i].n_rec / 6.0 * m->tp1[i].Nq * m->tp1[i].Nq * m->tp1[i].Nq};
+      }
+    } else {
+      if (phase == 1) break;
+      for (int i = 0; i < m->n_tp2; i++) it[n++] = {4, i, 2.0 * m->tp2[i].n_rec / 6.0 * m->tp2[i].Nq * m->tp2[i].Nq * m->tp2[i].Nq};
     }
-    int rc;
-    if (it[i].kind == 0) rc = launch_fast_bucket(m, fb[it[i].idx], u, Au, s);
-    else if (it[i].kind == 1) rc = d4b_launch_hp_bucket(m, it[i].idx, u, Au, s);
-    else rc = d4b_launch_generic(m, u, Au, m->generic_list, m->n_generic, s);
-    if (rc != D4B_OK) return rc;
-  }
-  for (int k = 0; k < used; k++) {
-    D4B_CUDA(cudaEventRecord(m->ev_join[k], m->side[k]));
-    D4B_CUDA(cudaStreamWaitEvent(st, m->ev_join[k], 0));
+    if (n == 0) continue;
+    for (int i = 1; i < n; i++) { item x = it[i]; int j = i; while (j > 0 && it[j - 1].w < x.w) { it[j] = it[j - 1]; j--; } it[j] = x; }
+    const bool fork = n > 1 && !serial && m->ev_fork;
+    int used = 0;
+    if (fork) D4B_CUDA(cudaEventRecord(m->ev_fork, st));
+    for (int i = 0; i < n; i++) {
+      cudaStream_t s = st;
+      if (fork && i > 0) {
+        const int k = (i - 1) % D4B_NSIDE;
+        s = m->side[k];
+        if (k >= used) { D4B_CUDA(cudaStreamWaitEvent(s, m->ev_fork, 0)); used = k + 1; }
+      }
+      int rc;
+      if (it[i].kind == 0) rc = launch_fast_bucket(m, fb[it[i].idx], u, Au, s);
+      else if (it[i].kind == 1) rc = d4b_launch_hp_bucket(m, it[i].idx, u, Au, s);
+      else if (it[i].kind == 2) rc = d4b_launch_generic(m, u, Au, m->generic_list, m->n_generic, s);
+      else rc = d4b_launch_tp_bucket(m, it[i].kind == 3 ? 1 : 2, it[i].idx, u, Au, s);
+      if (rc != D4B_OK) return rc;
+    }
+    for (int k = 0; k < used; k++) {
+      D4B_CUDA(cudaEventRecord(m->ev_join[k], m->side[k]));
+      D4B_CUDA(cudaStreamWaitEvent(st, m->ev_join[k], 0));
+    }
   }
   return D4B_OK;
 }

@@ -448,6 +448,307 @@ __global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_apply_hp_kernel(con
   for (int i = lane; i < N3; i += 32) Aue[i] = ACC[(i % N) + SJ * ((i / N) % N) + SK * (i / N2)];
 }
 
+/* ====================================================================================================
+ * Two-pass ("twin trace") form of the same operator for hp elements whose neighbours are all local.
+ * In the one-side-at-a-time formulation every half-mortar record evaluates BOTH sides of its mortar: its own
+ * trace (u-, sum_l a-_l du-/dr_l at the mortar points) and the neighbour's -- which is exactly the own-side trace
+ * of the neighbour's TWIN record (same mortar, roles swapped), with a+ = -a-(twin) at the same physical points
+ * (checked on every curved hp fixture: 2e-15 of the block maximum, hanging and mixed-p faces included).  So:
+ *   pass 1 (d4b_tp_trace_kernel): per element, volume term -> Au, and per record T/S1/QV of the OWN side only ->
+ *           W[record] = (u-, q-) at the mortar points (2 Nm^2 doubles, own point order);
+ *   pass 2 (d4b_tp_flux_kernel): per element and record, u+ = W[twin].u (reordered by tcode), q+ = -W[twin].q ->
+ *           FLUX -> BACK1/BACK2 -> Y, Z; LIFT onto the volume result; Au.
+ * The neighbour-side stages (run-time Np loops, the neighbour's whole element read from global memory per record)
+ * disappear; what is added is 2 Nm^2 doubles written and 4 Nm^2 read per record.  Elements with a ghost neighbour
+ * keep the single-pass kernel above (the twin's trace lives on another rank).  Pass 1 also runs, trace only, over
+ * the local neighbours of two-pass elements that are handled by other kernels. */
+struct tp_rec {        /* 48 bytes */
+  int64_t fac_off, g_off, w_own, w_twin;   /* w_twin < 0: boundary */
+  int32_t code;        /* bits 0-2 f_m, 6-8 tcode, 9-11 child_m+1, 15 boundary, 16 Robin */
+  int32_t dims;        /* Nm */
+  int64_t pad;
+};
+struct tp_slot { int64_t node_off, quad_off; int32_t rec_begin, nrec, flags, pad; };   /* flags bit 0: two-pass element */
+struct tp_args {
+  const tp_slot *slots; const tp_rec *recs; const double *G, *fac, *bc_g, *u; double *Au, *W;
+  int n_list, qt, NMX, per_warp;
+};
+__host__ __device__ static inline int tp1_scratch(int N, int NMX) { return 2 * N * N + 3 * NMX * N; }
+__host__ __device__ static inline int tp2_scratch(int N, int NMX) { return 3 * NMX * N + 4 * NMX * NMX; }
+
+template <int N, int Nq>
+__global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_tp_trace_kernel(const tp_args A)
+{
+  using L = HL<N, Nq>;
+  constexpr int N2 = L::N2, N3 = L::N3, Q2 = L::Q2, Q3 = L::Q3, NQ = L::NQ;
+  constexpr int SJ = L::SJ, SK = L::SK, AS = L::AS, BS = L::BS;
+  extern __shared__ double sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slot = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (slot >= A.n_list) return;
+  const hp_tab<N, Nq> &T = hp_const<N, Nq>::get();
+  const double *B = T.B, *C = T.C, *D = T.D;
+  double *U = sm + (size_t)warp * A.per_warp, *S = U + L::UA;
+  const tp_slot sl = A.slots[slot];
+  const double *ue = A.u + sl.node_off;
+  if (sl.flags & 1) {
+    const char *g = reinterpret_cast<const char *>(A.G + 6 * sl.quad_off);
+    for (int o = lane * 128; o < 6 * Q3 * 8; o += 32 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(g + o));
+  }
+  for (int r = lane >> 2; r < sl.nrec; r += 8) {
+    const tp_rec *h = A.recs + sl.rec_begin + r;
+    const int nm = __ldg(&h->dims), bytes = 3 * nm * nm * 8;
+    const char *p = reinterpret_cast<const char *>(A.fac + __ldg(&h->fac_off));
+    for (int o = (lane & 3) * 128; o < bytes; o += 4 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+  }
+  for (int i = lane; i < N3; i += 32) U[(i % N) + SJ * ((i / N) % N) + SK * (i / N2)] = ue[i];
+  __syncwarp();
+  /* ---------------- volume term of two-pass elements, straight to Au (same code as the single-pass kernel) */
+  if (sl.flags & 1) {
+    double *V0 = S, *V1 = S + L::AB, *V2 = S + 2 * L::AB, *V3 = V2 + L::BB, *V4 = V3 + L::BB;
+    for (int t = lane; t < N2; t += 32) {
+      const int i = t % N, j = t / N;
+      double x[N], y[Nq];
+      hld<N>(U + i + SJ * j, SK, x);
+      hmat<N, Nq, false>(B, x, y); hst<Nq>(V0 + t, AS, y);
+      hmat<N, Nq, false>(C, x, y); hst<Nq>(V1 + t, AS, y);
+    }
+    __syncwarp();
+    for (int t = lane; t < NQ; t += 32) {
+      const int i = t % N, c = t / N;
+      double x[N], y[Nq];
+      hld<N>(V0 + i + AS * c, N, x);
+      hmat<N, Nq, false>(B, x, y); hst<Nq>(V2 + i + N * c, BS, y);
+      hmat<N, Nq, false>(C, x, y); hst<Nq>(V3 + i + N * c, BS, y);
+      hld<N>(V1 + i + AS * c, N, x);
+      hmat<N, Nq, false>(B, x, y); hst<Nq>(V4 + i + N * c, BS, y);
+    }
+    __syncwarp();
+    const double *Ge = A.G + 6 * sl.quad_off;
+    for (int t = lane; t < Q2; t += 32) {
+      const int b = t % Nq, c = t / Nq;
+      double x[N], gr[Nq], gs[Nq], gt[Nq];
+      const int o = BS * b + N * c;
+      const double *Gt = Ge + Nq * t;
+      hld<N>(V2 + o, 1, x); hmat<N, Nq, false>(C, x, gr);
+      hld<N>(V3 + o, 1, x); hmat<N, Nq, false>(B, x, gs);
+      hld<N>(V4 + o, 1, x); hmat<N, Nq, false>(B, x, gt);
+#pragma unroll
+      for (int a = 0; a < Nq; a++) {
+        const double G00 = __ldg(Gt + a), G01 = __ldg(Gt + Q3 + a), G02 = __ldg(Gt + 2 * Q3 + a),
+                     G11 = __ldg(Gt + 3 * Q3 + a), G12 = __ldg(Gt + 4 * Q3 + a), G22 = __ldg(Gt + 5 * Q3 + a);
+        const double g0 = gr[a], g1 = gs[a], g2 = gt[a];
+        gr[a] = G00 * g0 + G01 * g1 + G02 * g2;
+        gs[a] = G01 * g0 + G11 * g1 + G12 * g2;
+        gt[a] = G02 * g0 + G12 * g1 + G22 * g2;
+      }
+      hmat<Nq, N, true>(C, gr, x); hst<N>(V2 + o, 1, x);
+      hmat<Nq, N, true>(B, gs, x); hst<N>(V3 + o, 1, x);
+      hmat<Nq, N, true>(B, gt, x); hst<N>(V4 + o, 1, x);
+    }
+    __syncwarp();
+    for (int t = lane; t < NQ; t += 32) {
+      const int i = t % N, c = t / N;
+      double x[Nq], y[N];
+      hld<Nq>(V2 + i + N * c, BS, x); hmat<Nq, N, true>(B, x, y);
+      hld<Nq>(V3 + i + N * c, BS, x); hmat_acc<Nq, N, true>(C, x, y);
+      hst<N>(V0 + i + AS * c, N, y);
+      hld<Nq>(V4 + i + N * c, BS, x); hmat<Nq, N, true>(B, x, y);
+      hst<N>(V1 + i + AS * c, N, y);
+    }
+    __syncwarp();
+    double *Aue = A.Au + sl.node_off;
+    for (int t = lane; t < N2; t += 32) {   /* transposed t-contraction: line (i,j) -> Au[t + N2 k] */
+      double x[Nq], y[N];
+      hld<Nq>(V0 + t, AS, x); hmat<Nq, N, true>(B, x, y);
+      hld<Nq>(V1 + t, AS, x); hmat_acc<Nq, N, true>(C, x, y);
+      hst<N>(Aue + t, N2, y);
+    }
+    __syncwarp();
+  }
+
+  /* ---------------- own-side traces of the records: T -> S1 -> QV -> W */
+  double *RA = S, *RB = S + 2 * N2;
+  const d4b_ops_dev &ops = c_hp_ops[A.qt];
+  const double *pool = ops.pool;
+#pragma unroll 1
+  for (int r = 0; r < sl.nrec; r++) {
+    const tp_rec R = A.recs[sl.rec_begin + r];
+    const int fm = R.code & 7, cm = ((R.code >> 9) & 7) - 1;
+    const int Nm = R.dims, Nm2 = Nm * Nm, mdq = Nm - 1;
+    const int d = fm >> 1, ia = d == 0 ? 1 : 0, ib = d == 2 ? 1 : 2;
+    const int ca = cm < 0 ? 0 : 1 + (cm & 1), cb = cm < 0 ? 0 : 1 + ((cm >> 1) & 1);
+    const double *Ea = pool + ops.idx.I[N - 1][mdq][ca], *EaD = pool + ops.idx.ID[N - 1][mdq][ca];
+    const double *Eb = pool + ops.idx.I[N - 1][mdq][cb], *EbD = pool + ops.idx.ID[N - 1][mdq][cb];
+    const double *F = A.fac + R.fac_off;
+    const int pl = Nm * N;
+    const int qrow = lane % Nm, qsub = lane / Nm, SQ = 32 / Nm;
+    {
+      int sa, sb, sn; hp_face_strides(d, SJ, SK, sa, sb, sn);
+      const int lay = (fm & 1) ? N - 1 : 0;
+      for (int t = lane; t < N2; t += 32) {
+        const int a = t % N, b = t / N;
+        double x[N]; hld<N>(U + a * sa + b * sb, sn, x);
+        double dn = 0.;
+#pragma unroll
+        for (int m = 0; m < N; m++) dn = fma(D[lay * N + m], x[m], dn);
+        RA[t] = (fm & 1) ? x[N - 1] : x[0];
+        RA[N2 + t] = dn;
+      }
+    }
+    __syncwarp();
+    if (qsub < SQ) {
+      double me[N], md[N];
+#pragma unroll
+      for (int i = 0; i < N; i++) { me[i] = __ldg(Ea + qrow * N + i); md[i] = __ldg(EaD + qrow * N + i); }
+      for (int b = qsub; b < N; b += SQ) {
+        double su = 0., sc = 0., sd = 0.;
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+          const double xu = RA[N * b + i], xn = RA[N2 + N * b + i];
+          su = fma(me[i], xu, su); sc = fma(md[i], xu, sc); sd = fma(me[i], xn, sd);
+        }
+        double *o = RB + qrow + Nm * b;
+        o[0] = su; o[pl] = sc; o[2 * pl] = sd;
+      }
+    }
+    __syncwarp();
+    if (qsub < SQ) {
+      double me[N], md[N];
+#pragma unroll
+      for (int i = 0; i < N; i++) { me[i] = __ldg(Eb + qrow * N + i); md[i] = __ldg(EbD + qrow * N + i); }
+      double *Wr = A.W + R.w_own;
+      for (int qa = qsub; qa < Nm; qa += SQ) {
+        double su = 0., sa = 0., sb = 0., sn = 0.;
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+          const double x1 = RB[qa + Nm * i], x2 = RB[pl + qa + Nm * i], x3 = RB[2 * pl + qa + Nm * i];
+          su = fma(me[i], x1, su); sa = fma(me[i], x2, sa); sb = fma(md[i], x1, sb); sn = fma(me[i], x3, sn);
+        }
+        const int q = qa + Nm * qrow;
+        Wr[q] = su;
+        Wr[Nm2 + q] = __ldg(F + ia * Nm2 + q) * sa + __ldg(F + ib * Nm2 + q) * sb + __ldg(F + d * Nm2 + q) * sn;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+template <int N, int Nq>
+__global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_tp_flux_kernel(const tp_args A)
+{
+  using L = HL<N, Nq>;
+  constexpr int N2 = L::N2, N3 = L::N3, SJ = L::SJ, SK = L::SK;
+  extern __shared__ double sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slot = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (slot >= A.n_list) return;
+  const hp_tab<N, Nq> &T = hp_const<N, Nq>::get();
+  const double *D = T.D;
+  double *ACC = sm + (size_t)warp * A.per_warp, *YZ = ACC + L::UA, *RA = YZ + 12 * N2, *RB = RA + 3 * A.NMX * N;
+  const tp_slot sl = A.slots[slot];
+  for (int i = lane; i < 12 * N2; i += 32) YZ[i] = 0.;
+  const d4b_ops_dev &ops = c_hp_ops[A.qt];
+  const double *pool = ops.pool;
+#pragma unroll 1
+  for (int r = 0; r < sl.nrec; r++) {
+    const tp_rec R = A.recs[sl.rec_begin + r];
+    const int fm = R.code & 7, tc = (R.code >> 6) & 7, cm = ((R.code >> 9) & 7) - 1;
+    const bool bnd = (R.code >> 15) & 1;
+    const int Nm = R.dims, Nm2 = Nm * Nm, mdq = Nm - 1;
+    const int d = fm >> 1;
+    const int ca = cm < 0 ? 0 : 1 + (cm & 1), cb = cm < 0 ? 0 : 1 + ((cm >> 1) & 1);
+    const double *Ea = pool + ops.idx.I[N - 1][mdq][ca], *EaD = pool + ops.idx.ID[N - 1][mdq][ca];
+    const double *Eb = pool + ops.idx.I[N - 1][mdq][cb], *EbD = pool + ops.idx.ID[N - 1][mdq][cb];
+    const double *F = A.fac + R.fac_off;
+    const double *Wo = A.W + R.w_own, *Wt = A.W + (bnd ? R.w_own : R.w_twin);
+    /* FLUX at the mortar quadrature points (..._flux_sipg.c:645-677 interior, :139-191 Dirichlet, :377-476 Robin) */
+    {
+      const double *wq = pool + ops.idx.w[mdq];
+      for (int q = lane; q < Nm2; q += 32) {
+        const int b = q / Nm, a = q - b * Nm;
+        const double w = __ldg(wq + a) * __ldg(wq + b);
+        const double am0 = __ldg(F + q), am1 = __ldg(F + Nm2 + q), am2 = __ldg(F + 2 * Nm2 + q);
+        const double um = __ldg(Wo + q), qm = __ldg(Wo + Nm2 + q);
+        double jump, t1, sjs, hs;
+        if (!bnd) {
+          const int qp = hp_tcode_src(tc, Nm, a, b);   /* my point in the twin's point order */
+          jump = um - __ldg(Wt + qp); t1 = -0.5 * (qm - __ldg(Wt + Nm2 + qp)); sjs = __ldg(F + 6 * Nm2 + q); hs = -0.5;
+        } else {
+          const double gv = R.g_off >= 0 ? __ldg(A.bc_g + R.g_off + q) : 0.;
+          jump = um - gv; t1 = -qm; sjs = __ldg(F + 3 * Nm2 + q); hs = -1.0;
+          if ((R.code >> 16) & 1) {
+            RB[q] = w * (sjs * um - gv); RB[Nm2 + q] = 0.; RB[2 * Nm2 + q] = 0.; RB[3 * Nm2 + q] = 0.;
+            continue;
+          }
+        }
+        const double wj = w * hs * jump;
+        RB[q] = w * (t1 + sjs * jump);
+        RB[Nm2 + q] = wj * (d == 0 ? am1 : am0);
+        RB[2 * Nm2 + q] = wj * (d == 2 ? am1 : am2);
+        RB[3 * Nm2 + q] = wj * (d == 0 ? am0 : (d == 1 ? am1 : am2));
+      }
+    }
+    __syncwarp();
+    const int NmN = Nm * N;
+    constexpr int SN = 32 / N;
+    const int jrow = lane % N, jsub = lane / N;
+    if (jsub < SN) {
+      for (int qa = jsub; qa < Nm; qa += SN) {
+        double x1 = 0., ha = 0., hn = 0.;
+        const double *f0 = RB + qa;
+#pragma unroll 4
+        for (int qb = 0; qb < Nm; qb++) {
+          const double e = __ldg(Eb + qb * N + jrow), ed = __ldg(EbD + qb * N + jrow);
+          const double v0 = f0[Nm * qb], v1 = f0[Nm2 + Nm * qb], v2 = f0[2 * Nm2 + Nm * qb], v3 = f0[3 * Nm2 + Nm * qb];
+          x1 = fma(e, v0, x1); x1 = fma(ed, v2, x1); ha = fma(e, v1, ha); hn = fma(e, v3, hn);
+        }
+        double *o = RA + qa + Nm * jrow;
+        o[0] = x1; o[NmN] = ha; o[2 * NmN] = hn;
+      }
+    }
+    __syncwarp();
+    if (jsub < SN) {
+      double *yz = YZ + fm * 2 * N2;
+      for (int bp = jsub; bp < N; bp += SN) {
+        double y = 0., z = 0.;
+        const double *x1 = RA + Nm * bp;
+#pragma unroll 4
+        for (int qa = 0; qa < Nm; qa++) {
+          const double e = __ldg(Ea + qa * N + jrow), ed = __ldg(EaD + qa * N + jrow);
+          y = fma(e, x1[qa], y); y = fma(ed, x1[NmN + qa], y); z = fma(e, x1[2 * NmN + qa], z);
+        }
+        yz[jrow + N * bp] += y; yz[N2 + jrow + N * bp] += z;
+      }
+    }
+    __syncwarp();
+  }
+  /* LIFT onto the volume result that pass 1 left in Au */
+  double *Aue = A.Au + sl.node_off;
+  for (int i = lane; i < N3; i += 32) ACC[(i % N) + SJ * ((i / N) % N) + SK * (i / N2)] = Aue[i];
+  __syncwarp();
+#pragma unroll 1
+  for (int d = 0; d < 3; d++) {
+    int sa, sb, sn; hp_face_strides(d, SJ, SK, sa, sb, sn);
+    for (int t = lane; t < N2; t += 32) {
+      double *acc = ACC + (t % N) * sa + (t / N) * sb;
+      const double y0 = YZ[(4 * d) * N2 + t], z0 = YZ[(4 * d + 1) * N2 + t];
+      const double y1 = YZ[(4 * d + 2) * N2 + t], z1 = YZ[(4 * d + 3) * N2 + t];
+#pragma unroll
+      for (int m = 0; m < N; m++) {
+        double v = acc[m * sn] + D[m] * z0 + D[(N - 1) * N + m] * z1;
+        if (m == 0) v += y0;
+        if (m == N - 1) v += y1;
+        acc[m * sn] = v;
+      }
+    }
+    __syncwarp();
+  }
+  for (int i = lane; i < N3; i += 32) Aue[i] = ACC[(i % N) + SJ * ((i / N) % N) + SK * (i / N2)];
+}
+
+
+
 /* ------------------------------------------------------------------ host side */
 struct hp_bucket_host { std::vector<hp_slot> slots; std::vector<hp_rec> recs; int NMX = 0, MX = 0; };
 
@@ -474,15 +775,51 @@ static size_t hp_warp_doubles_rt(int N, int Nq, int NMX, int MX)
   return (size_t)1 << 40;
 }
 
-/* Take the elements of `cand` the templated hp kernel can run (instance exists, neighbour N <= HP_MAXNP,
+int d4b_opt_tp_min();
+struct tp_bucket_host { std::vector<tp_slot> slots; std::vector<tp_rec> recs; int NMX = 0; };
+
+static int tp_upload(tp_bucket_host *hb, d4b_tp_bucket *out, int *n_out)
+{
+  *n_out = 0;
+  for (int k = 0; k < D4B_NDEG * D4B_NDEGQ; k++) {
+    tp_bucket_host &b = hb[k];
+    if (b.slots.empty()) continue;
+    if (*n_out == D4B_MAX_BUCKETS) { d4b_set_error("more than %d (deg, deg_quad) pairs on one level", D4B_MAX_BUCKETS); return D4B_EINVAL; }
+    d4b_tp_bucket &o = out[(*n_out)++];
+    o.N = k / D4B_NDEGQ + 1; o.Nq = k % D4B_NDEGQ + 1; o.count = (int)b.slots.size(); o.NMX = b.NMX; o.n_rec = (int)b.recs.size();
+    D4B_CUDA(cudaMalloc(&o.slots, b.slots.size() * sizeof(tp_slot)));
+    D4B_CUDA(cudaMemcpy(o.slots, b.slots.data(), b.slots.size() * sizeof(tp_slot), cudaMemcpyHostToDevice));
+    D4B_CUDA(cudaMalloc(&o.recs, (b.recs.size() ? b.recs.size() : 1) * sizeof(tp_rec)));
+    if (!b.recs.empty()) D4B_CUDA(cudaMemcpy(o.recs, b.recs.data(), b.recs.size() * sizeof(tp_rec), cudaMemcpyHostToDevice));
+  }
+  return D4B_OK;
+}
+
+/* the record of the neighbour that shares the mortar of record r of element e (roles swapped), or -1 */
+static int tp_find_twin(const d4b_mesh_desc_t *D, int e, int r)
+{
+  const d4b_hm_t &h = D->hm[r];
+  const int p = h.nbr;
+  for (int q = D->hm_begin[p]; q < D->hm_begin[p + 1]; q++) {
+    const d4b_hm_t &g = D->hm[q];
+    if (g.nbr == e && g.f_m == h.f_p && g.f_p == h.f_m && g.child_m == h.child_p && g.child_p == h.child_m && g.degq == h.degq) return q;
+  }
+  return -1;
+}
+
+/* Take the elements of `cand` the templated hp kernels can run (instance exists, neighbour N <= HP_MAXNP,
  * mortar points <= HP_MAXNM, one warp's scratch fits) into (N, Nq) buckets with resolved per-record
- * metadata; the others are appended to `rest` (completeness kernel). */
+ * metadata; the others are appended to `rest` (completeness kernel).  Elements whose neighbours are all local
+ * (and have a trace instance) take the two-pass path when the level has enough of them to pay for the second
+ * round of launches; the rest (ghost neighbours, small levels) the single-pass kernel. */
 int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_t> &cand, std::vector<int32_t> &rest)
 {
-  m->n_hp = 0;
+  m->n_hp = 0; m->n_tp1 = m->n_tp2 = 0; m->tpW = nullptr; m->tpW_doubles = 0;
   if (!D->hm) { rest.insert(rest.end(), cand.begin(), cand.end()); return D4B_OK; }
   std::vector<hp_bucket_host> hb(D4B_NDEG * D4B_NDEGQ);
   const int nl = m->n_local;
+  struct elig { int32_t e; int nmx, mx; };
+  std::vector<elig> el;
   for (int32_t e : cand) {
     const int N = D->deg[e] + 1, Nq = D->degq[e] + 1;
     bool ok = d4b_hp_supported(N, Nq);
@@ -496,6 +833,33 @@ int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_
     }
     if (ok && hp_warp_doubles_rt(N, Nq, nmx, mx) * 8 > 200 * 1024) ok = false;
     if (!ok) { rest.push_back(e); continue; }
+    el.push_back({e, nmx, mx});
+  }
+  /* ---- which of them take the two-pass path */
+  const int tp_min = d4b_opt_tp_min();   /* option two_pass_min_elements (D4B_TP_MIN; D4B_NO_TP = never) */
+  const bool no_tp = tp_min == 0x7fffffff;
+  std::vector<char> is_tp(nl, 0);
+  std::vector<int32_t> twin(D->hm_begin[nl], -1);
+  int n_tp = 0;
+  if (!no_tp) {
+    for (const elig &x : el) {
+      const int e = x.e;
+      bool ok = true;
+      for (int r = D->hm_begin[e]; ok && r < D->hm_begin[e + 1]; r++) {
+        const d4b_hm_t &h = D->hm[r];
+        if (h.nbr < 0) continue;
+        if (h.nbr >= nl || !d4b_hp_supported(D->deg[h.nbr] + 1, D->degq[h.nbr] + 1)) { ok = false; break; }
+        if ((twin[r] = tp_find_twin(D, e, r)) < 0) ok = false;
+      }
+      if (ok) { is_tp[e] = 1; n_tp++; }
+    }
+    if (n_tp < tp_min) { std::fill(is_tp.begin(), is_tp.end(), 0); n_tp = 0; }
+  }
+  /* ---- single-pass buckets */
+  for (const elig &x : el) {
+    const int e = x.e;
+    if (is_tp[e]) continue;
+    const int N = D->deg[e] + 1, Nq = D->degq[e] + 1, nmx = x.nmx, mx = x.mx;
     hp_bucket_host &b = hb[(N - 1) * D4B_NDEGQ + (Nq - 1)];
     hp_slot s; s.node_off = D->node_off[e]; s.quad_off = D->quad_off[e];
     s.rec_begin = (int32_t)b.recs.size(); s.nrec = D->hm_begin[e + 1] - D->hm_begin[e]; s.pad = 0;
@@ -529,6 +893,48 @@ int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_
     D4B_CUDA(cudaMalloc(&o.recs, b.recs.size() * sizeof(hp_rec)));
     D4B_CUDA(cudaMemcpy(o.recs, b.recs.data(), b.recs.size() * sizeof(hp_rec), cudaMemcpyHostToDevice));
   }
+  if (!n_tp) return D4B_OK;
+  /* ---- two-pass tables.  W slots: every record of a two-pass element + the twins of its interior records */
+  std::vector<int64_t> w_of(D->hm_begin[nl], -1);
+  int64_t wn = 0;
+  auto want = [&](int r) { if (w_of[r] < 0) { const int nm = D->hm[r].degq + 1; w_of[r] = wn; wn += 2 * nm * nm; } };
+  for (int e = 0; e < nl; e++) {
+    if (!is_tp[e]) continue;
+    for (int r = D->hm_begin[e]; r < D->hm_begin[e + 1]; r++) { want(r); if (twin[r] >= 0) want(twin[r]); }
+  }
+  std::vector<tp_bucket_host> b1(D4B_NDEG * D4B_NDEGQ), b2(D4B_NDEG * D4B_NDEGQ);
+  for (int e = 0; e < nl; e++) {
+    int nw = 0;
+    for (int r = D->hm_begin[e]; r < D->hm_begin[e + 1]; r++) nw += w_of[r] >= 0;
+    if (!nw) continue;
+    const int N = D->deg[e] + 1, Nq = D->degq[e] + 1;
+    tp_bucket_host &t1 = b1[(N - 1) * D4B_NDEGQ + (Nq - 1)];
+    tp_slot s1; s1.node_off = D->node_off[e]; s1.quad_off = D->quad_off[e]; s1.rec_begin = (int32_t)t1.recs.size(); s1.nrec = nw;
+    s1.flags = is_tp[e]; s1.pad = 0;
+    tp_bucket_host *t2 = is_tp[e] ? &b2[(N - 1) * D4B_NDEGQ + (Nq - 1)] : nullptr;
+    tp_slot s2 = s1;
+    if (t2) { s2.rec_begin = (int32_t)t2->recs.size(); s2.nrec = D->hm_begin[e + 1] - D->hm_begin[e]; }
+    if (Nq > t1.NMX) t1.NMX = Nq;
+    for (int r = D->hm_begin[e]; r < D->hm_begin[e + 1]; r++) {
+      if (w_of[r] < 0) continue;
+      const d4b_hm_t &h = D->hm[r];
+      const int bnd = h.nbr < 0, Nm = h.degq + 1;
+      tp_rec R; R.fac_off = h.fac_off; R.g_off = h.g_off; R.w_own = w_of[r]; R.w_twin = bnd ? -1 : (twin[r] >= 0 ? w_of[twin[r]] : -1);
+      R.code = (h.f_m & 7) | ((h.tcode & 7) << 6) | ((h.child_m + 1) << 9) | (bnd << 15) | ((bnd && h.pad == 1) << 16);
+      R.dims = Nm; R.pad = 0;
+      if (Nm < N || Nm > HP_MAXNM) { d4b_set_error("two-pass hp path: mortar of %d points on an element with N = %d", Nm, N); return D4B_EINVAL; }
+      t1.recs.push_back(R);
+      if (Nm > t1.NMX) t1.NMX = Nm;
+      if (t2) { t2->recs.push_back(R); if (Nm > t2->NMX) t2->NMX = Nm; }
+    }
+    t1.slots.push_back(s1);
+    if (t2) t2->slots.push_back(s2);
+  }
+  int rc;
+  if ((rc = tp_upload(b1.data(), m->tp1, &m->n_tp1)) != D4B_OK) return rc;
+  if ((rc = tp_upload(b2.data(), m->tp2, &m->n_tp2)) != D4B_OK) return rc;
+  D4B_CUDA(cudaMalloc((void **)&m->tpW, (size_t)(wn ? wn : 1) * sizeof(double)));
+  m->tpW_doubles = wn;
   return D4B_OK;
 }
 
@@ -544,30 +950,35 @@ static int hp_bind_ops(int qt)
   return D4B_OK;
 }
 
+/* the element's own tables live in a __constant__ block of the (N, Nq) instance: written once; a level with the
+ * other quadrature type waits for everything in flight before it is replaced */
+template <int N, int Nq> static int hp_ensure_tab(int qt)
+{
+  static int have_qt = -1;
+  if (have_qt == qt) return D4B_OK;
+  if (have_qt != -1) D4B_CUDA(cudaDeviceSynchronize());
+  hp_tab<N, Nq> t;
+  double I[D4B_OPS_MAXN * D4B_OPS_MAXN], Dm[D4B_OPS_MAXN * D4B_OPS_MAXN];
+  d4b_ops_interp(N - 1, Nq - 1, qt, -1, I); d4b_ops_diff(N - 1, Dm);
+  for (int q = 0; q < Nq; q++)
+    for (int j = 0; j < N; j++) {
+      t.B[q * N + j] = I[q * N + j];
+      double s = 0.;
+      for (int k = 0; k < N; k++) s += I[q * N + k] * Dm[k * N + j];
+      t.C[q * N + j] = s;
+    }
+  for (int i = 0; i < N * N; i++) t.D[i] = Dm[i];
+  D4B_CUDA((hp_const<N, Nq>::put(&t)));
+  D4B_CUDA(cudaDeviceSynchronize());   /* the staged copy has landed before any stream launches */
+  have_qt = qt;
+  return D4B_OK;
+}
+
 template <int N, int Nq>
 static int hp_launch_bucket(const d4b_mesh *m, const d4b_hp_bucket &b, const double *u, double *Au, cudaStream_t st)
 {
-  /* the element's own tables live in a __constant__ block of this instance: written once; a level with the
-   * other quadrature type waits for everything in flight before it is replaced */
-  static int have_qt = -1;
   static size_t attr_smem = 0;
-  if (have_qt != m->quad_type) {
-    if (have_qt != -1) D4B_CUDA(cudaDeviceSynchronize());
-    hp_tab<N, Nq> t;
-    double I[D4B_OPS_MAXN * D4B_OPS_MAXN], Dm[D4B_OPS_MAXN * D4B_OPS_MAXN];
-    d4b_ops_interp(N - 1, Nq - 1, m->quad_type, -1, I); d4b_ops_diff(N - 1, Dm);
-    for (int q = 0; q < Nq; q++)
-      for (int j = 0; j < N; j++) {
-        t.B[q * N + j] = I[q * N + j];
-        double s = 0.;
-        for (int k = 0; k < N; k++) s += I[q * N + k] * Dm[k * N + j];
-        t.C[q * N + j] = s;
-      }
-    for (int i = 0; i < N * N; i++) t.D[i] = Dm[i];
-    D4B_CUDA((hp_const<N, Nq>::put(&t)));
-    D4B_CUDA(cudaDeviceSynchronize());   /* the staged copy has landed before any stream launches */
-    have_qt = m->quad_type;
-  }
+  { int rct = hp_ensure_tab<N, Nq>(m->quad_type); if (rct != D4B_OK) return rct; }
   const size_t per_warp = hp_warp_doubles<N, Nq>(b.NMX, b.MX);
   int wpb = 4;
   while (wpb > 1 && wpb * per_warp * 8 > 110 * 1024) wpb >>= 1;   /* at least two CTAs per SM */
@@ -593,6 +1004,46 @@ int d4b_launch_hp_bucket(const d4b_mesh *m, int i, const double *u, double *Au, 
   const d4b_hp_bucket &b = m->hp[i];
   rc = D4B_EINVAL;
 #define X(a, c, g) if (b.N == a && b.Nq == c) rc = hp_launch_bucket<a, c>(m, b, u, Au, st);
+  HP_PAIRS(X)
+#undef X
+  return rc;
+}
+
+template <int N, int Nq>
+static int tp_launch_bucket(const d4b_mesh *m, int pass, const d4b_tp_bucket &b, const double *u, double *Au, cudaStream_t st)
+{
+  using L = HL<N, Nq>;
+  static size_t attr_smem[2] = {0, 0};
+  { int rct = hp_ensure_tab<N, Nq>(m->quad_type); if (rct != D4B_OK) return rct; }
+  size_t per_warp;
+  if (pass == 1) { int scr = tp1_scratch(N, b.NMX); if (scr < L::VOL) scr = L::VOL; per_warp = (size_t)L::UA + scr; }
+  else per_warp = (size_t)L::UA + 12 * L::N2 + tp2_scratch(N, b.NMX);
+  int wpb = 4;
+  while (wpb > 1 && wpb * per_warp * 8 > 110 * 1024) wpb >>= 1;
+  const size_t smem = wpb * per_warp * 8;
+  if (smem > attr_smem[pass - 1]) {
+    if (pass == 1) D4B_CUDA(cudaFuncSetAttribute(d4b_tp_trace_kernel<N, Nq>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else D4B_CUDA(cudaFuncSetAttribute(d4b_tp_flux_kernel<N, Nq>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_smem[pass - 1] = smem;
+  }
+  tp_args A;
+  A.slots = (const tp_slot *)b.slots; A.recs = (const tp_rec *)b.recs; A.G = m->G; A.fac = m->fac; A.bc_g = m->bc_g;
+  A.u = u; A.Au = Au; A.W = m->tpW; A.n_list = b.count; A.qt = m->quad_type; A.NMX = b.NMX; A.per_warp = (int)per_warp;
+  const int grid = (b.count + wpb - 1) / wpb;
+  if (pass == 1) d4b_tp_trace_kernel<N, Nq><<<grid, 32 * wpb, smem, st>>>(A);
+  else d4b_tp_flux_kernel<N, Nq><<<grid, 32 * wpb, smem, st>>>(A);
+  D4B_CUDA(cudaGetLastError());
+  d4b_count_launch(1);
+  return D4B_OK;
+}
+
+int d4b_launch_tp_bucket(const d4b_mesh *m, int pass, int i, const double *u, double *Au, cudaStream_t st)
+{
+  int rc = hp_bind_ops(m->quad_type);
+  if (rc != D4B_OK) return rc;
+  const d4b_tp_bucket &b = pass == 1 ? m->tp1[i] : m->tp2[i];
+  rc = D4B_EINVAL;
+#define X(a, c, g) if (b.N == a && b.Nq == c) rc = tp_launch_bucket<a, c>(m, pass, b, u, Au, st);
   HP_PAIRS(X)
 #undef X
   return rc;

@@ -38,6 +38,12 @@ struct d4b_hp_bucket {
   void *slots, *recs;                 /* device: hp_slot[count], hp_rec[n_rec]                          */
 };
 
+/* one (N, Nq) bucket of the two-pass (twin-trace) hp kernels (d4b_apply_hp.cu): pass 1 or pass 2 */
+struct d4b_tp_bucket {
+  int N, Nq, count, n_rec, NMX;
+  void *slots, *recs;                 /* device: tp_slot[count], tp_rec[n_rec] */
+};
+
 /* device-resident mesh level */
 struct d4b_mesh {
   int n_local, n_ghost, quad_type, max_deg, max_degq, max_deg_ext, max_degq_own;
@@ -64,6 +70,8 @@ struct d4b_mesh {
   #define D4B_NSIDE 6
   cudaStream_t side[D4B_NSIDE]; cudaEvent_t ev_fork, ev_join[D4B_NSIDE];   /* concurrent bucket launches of one apply */
   int32_t *generic_list; int n_generic;   /* elements left to the generic kernel */
+  /* two-pass hp path: trace buckets (pass 1), flux buckets (pass 2), trace buffer W (2 Nm^2 doubles per record) */
+  d4b_tp_bucket tp1[D4B_MAX_BUCKETS], tp2[D4B_MAX_BUCKETS]; int n_tp1, n_tp2; double *tpW; int64_t tpW_doubles;
   /* halo / compute overlap of a distributed apply (d4b_apply_dev): every regular bucket is split once into the
    * batches that touch no ghost element (launched while the exchange runs on comm_stream) and the rest */
   int split_built;                 /* 0 not yet, 1 built, -1 nothing to overlap (no ghost-free regular batch) */
@@ -95,6 +103,7 @@ void d4b_count_launch(int n);
 bool d4b_fast_supported(int N, int Nq);
 bool d4b_hp_supported(int N, int Nq);
 int d4b_launch_hp_bucket(const d4b_mesh *m, int i, const double *u, double *Au, cudaStream_t st);
+int d4b_launch_tp_bucket(const d4b_mesh *m, int pass, int i, const double *u, double *Au, cudaStream_t st);
 bool d4b_v3_supported(int N, int Nq);
 int d4b_launch_v3(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st);
 int d4b_launch_v3_range(const d4b_mesh *m, const d4b_fast_bucket &b, const double *u, double *Au, cudaStream_t st,

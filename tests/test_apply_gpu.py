@@ -22,7 +22,7 @@ def all_fixtures():
     fs = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "*.fix")))
     fs += sorted(glob.glob(os.path.join(ROOT, "oracle", "_ref", "fixtures", "*.fix")))
     # single-level apply fixtures only (not the 1-D table dump, not the multigrid fixtures)
-    return [f for f in fs if not os.path.basename(f).startswith(("ref_ops", "mg_"))]
+    return [f for f in fs if not os.path.basename(f).startswith(("ref_ops", "mg_", "amr_"))]
 
 
 @pytest.mark.parametrize("path", all_fixtures(), ids=lambda p: os.path.basename(p)[:-4])
@@ -43,8 +43,12 @@ def test_hp_kernel_matches_reference_on_every_element_class(path):
     the register-blocked / line-task kernels, the others in the hp kernel) against the completeness kernel."""
     fx = fixture.load(path)
     out, split = {}, {}
-    for key, env in (("default", {}), ("all_hp", {"D4B_ALL_HP": "1"}), ("no_hp", {"D4B_NO_HP": "1"})):
+    L = d4est_b200.lib()
+    for key, env in (("default", {}), ("all_hp", {"D4B_ALL_HP": "1"}), ("no_hp", {"D4B_NO_HP": "1"}),
+                     ("two_pass", {}), ("all_hp_two_pass", {"D4B_ALL_HP": "1"})):
         os.environ.update(env)
+        # the two-pass (twin-trace) hp kernels are chosen for levels with >= 4096 such elements: force them here
+        d4est_b200.capi.check(L.d4b_set_option(b"two_pass_min_elements", 0 if "two_pass" in key else 1 << 30))
         try:
             lvl = d4est_b200.MeshLevel(fx)
             split[key] = lvl.kernel_split
@@ -53,9 +57,12 @@ def test_hp_kernel_matches_reference_on_every_element_class(path):
                 assert np.array_equal(out[key], lvl.apply_host(fx["u"]))   # fixed accumulation order
             lvl.close()
         finally:
+            d4est_b200.capi.check(L.d4b_set_option(b"two_pass_min_elements", 4096))
             for k in env:
                 del os.environ[k]
     nl = int(fx["hdr"][0])
+    assert split["all_hp_two_pass"][1] == nl
+    assert rel(out["all_hp_two_pass"], out["all_hp"]) < 1e-13   # a+ = -a-(twin): equal to rounding, not bitwise
     assert split["all_hp"][0] == 0 and split["no_hp"][1] == 0
     assert split["all_hp"][1] == nl, split        # every (N, Nq) of the fixtures has an instance
     assert split["default"][2] == 0, split        # nothing is left to the completeness kernel
