@@ -476,6 +476,74 @@ struct tp_args {
 __host__ __device__ static inline int tp1_scratch(int N, int NMX) { return 2 * N * N + 3 * NMX * N; }
 __host__ __device__ static inline int tp2_scratch(int N, int NMX) { return 3 * NMX * N + 4 * NMX * NMX; }
 
+/* own-side traces of one record; NMT = number of mortar points per direction when known at compile time (0: run time) */
+template <int N, int Nq, int NMT>
+__device__ __forceinline__ void tp_trace_record(const tp_args &A, const tp_rec &R, const double *U, double *RA, double *RB,
+                                                const double *D, int lane)
+{
+  using L = HL<N, Nq>;
+  constexpr int N2 = L::N2, SJ = L::SJ, SK = L::SK;
+  const d4b_ops_dev &ops = c_hp_ops[A.qt];
+  const double *pool = ops.pool;
+  const int fm = R.code & 7, cm = ((R.code >> 9) & 7) - 1;
+  const int Nm = NMT ? NMT : R.dims, Nm2 = Nm * Nm, mdq = Nm - 1;
+  const int d = fm >> 1, ia = d == 0 ? 1 : 0, ib = d == 2 ? 1 : 2;
+  const int ca = cm < 0 ? 0 : 1 + (cm & 1), cb = cm < 0 ? 0 : 1 + ((cm >> 1) & 1);
+  const double *Ea = pool + ops.idx.I[N - 1][mdq][ca], *EaD = pool + ops.idx.ID[N - 1][mdq][ca];
+  const double *Eb = pool + ops.idx.I[N - 1][mdq][cb], *EbD = pool + ops.idx.ID[N - 1][mdq][cb];
+  const double *F = A.fac + R.fac_off;
+  const int pl = Nm * N;
+  const int qrow = lane % Nm, qsub = lane / Nm, SQ = 32 / Nm;
+  {
+    int sa, sb, sn; hp_face_strides(d, SJ, SK, sa, sb, sn);
+    const int lay = (fm & 1) ? N - 1 : 0;
+    for (int t = lane; t < N2; t += 32) {
+      const int a = t % N, b = t / N;
+      double x[N]; hld<N>(U + a * sa + b * sb, sn, x);
+      double dn = 0.;
+#pragma unroll
+      for (int m = 0; m < N; m++) dn = fma(D[lay * N + m], x[m], dn);
+      RA[t] = (fm & 1) ? x[N - 1] : x[0];
+      RA[N2 + t] = dn;
+    }
+  }
+  __syncwarp();
+  if (qsub < SQ) {
+    double me[N], md[N];
+#pragma unroll
+    for (int i = 0; i < N; i++) { me[i] = __ldg(Ea + qrow * N + i); md[i] = __ldg(EaD + qrow * N + i); }
+    for (int b = qsub; b < N; b += SQ) {
+      double su = 0., sc = 0., sd = 0.;
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const double xu = RA[N * b + i], xn = RA[N2 + N * b + i];
+        su = fma(me[i], xu, su); sc = fma(md[i], xu, sc); sd = fma(me[i], xn, sd);
+      }
+      double *o = RB + qrow + Nm * b;
+      o[0] = su; o[pl] = sc; o[2 * pl] = sd;
+    }
+  }
+  __syncwarp();
+  if (qsub < SQ) {
+    double me[N], md[N];
+#pragma unroll
+    for (int i = 0; i < N; i++) { me[i] = __ldg(Eb + qrow * N + i); md[i] = __ldg(EbD + qrow * N + i); }
+    double *Wr = A.W + R.w_own;
+    for (int qa = qsub; qa < Nm; qa += SQ) {
+      double su = 0., sa = 0., sb = 0., sn = 0.;
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const double x1 = RB[qa + Nm * i], x2 = RB[pl + qa + Nm * i], x3 = RB[2 * pl + qa + Nm * i];
+        su = fma(me[i], x1, su); sa = fma(me[i], x2, sa); sb = fma(md[i], x1, sb); sn = fma(me[i], x3, sn);
+      }
+      const int q = qa + Nm * qrow;
+      Wr[q] = su;
+      Wr[Nm2 + q] = __ldg(F + ia * Nm2 + q) * sa + __ldg(F + ib * Nm2 + q) * sb + __ldg(F + d * Nm2 + q) * sn;
+    }
+  }
+  __syncwarp();
+}
+
 template <int N, int Nq>
 __global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_tp_trace_kernel(const tp_args A)
 {
@@ -569,69 +637,95 @@ __global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_tp_trace_kernel(con
 
   /* ---------------- own-side traces of the records: T -> S1 -> QV -> W */
   double *RA = S, *RB = S + 2 * N2;
-  const d4b_ops_dev &ops = c_hp_ops[A.qt];
-  const double *pool = ops.pool;
 #pragma unroll 1
   for (int r = 0; r < sl.nrec; r++) {
     const tp_rec R = A.recs[sl.rec_begin + r];
-    const int fm = R.code & 7, cm = ((R.code >> 9) & 7) - 1;
-    const int Nm = R.dims, Nm2 = Nm * Nm, mdq = Nm - 1;
-    const int d = fm >> 1, ia = d == 0 ? 1 : 0, ib = d == 2 ? 1 : 2;
-    const int ca = cm < 0 ? 0 : 1 + (cm & 1), cb = cm < 0 ? 0 : 1 + ((cm >> 1) & 1);
-    const double *Ea = pool + ops.idx.I[N - 1][mdq][ca], *EaD = pool + ops.idx.ID[N - 1][mdq][ca];
-    const double *Eb = pool + ops.idx.I[N - 1][mdq][cb], *EbD = pool + ops.idx.ID[N - 1][mdq][cb];
-    const double *F = A.fac + R.fac_off;
-    const int pl = Nm * N;
-    const int qrow = lane % Nm, qsub = lane / Nm, SQ = 32 / Nm;
-    {
-      int sa, sb, sn; hp_face_strides(d, SJ, SK, sa, sb, sn);
-      const int lay = (fm & 1) ? N - 1 : 0;
-      for (int t = lane; t < N2; t += 32) {
-        const int a = t % N, b = t / N;
-        double x[N]; hld<N>(U + a * sa + b * sb, sn, x);
-        double dn = 0.;
-#pragma unroll
-        for (int m = 0; m < N; m++) dn = fma(D[lay * N + m], x[m], dn);
-        RA[t] = (fm & 1) ? x[N - 1] : x[0];
-        RA[N2 + t] = dn;
-      }
+    switch (R.dims - Nq) {
+      case 0: tp_trace_record<N, Nq, Nq>(A, R, U, RA, RB, D, lane); break;
+      case 1: tp_trace_record<N, Nq, Nq + 1>(A, R, U, RA, RB, D, lane); break;
+      case 2: tp_trace_record<N, Nq, Nq + 2>(A, R, U, RA, RB, D, lane); break;
+      default: tp_trace_record<N, Nq, 0>(A, R, U, RA, RB, D, lane); break;
     }
-    __syncwarp();
-    if (qsub < SQ) {
-      double me[N], md[N];
-#pragma unroll
-      for (int i = 0; i < N; i++) { me[i] = __ldg(Ea + qrow * N + i); md[i] = __ldg(EaD + qrow * N + i); }
-      for (int b = qsub; b < N; b += SQ) {
-        double su = 0., sc = 0., sd = 0.;
-#pragma unroll
-        for (int i = 0; i < N; i++) {
-          const double xu = RA[N * b + i], xn = RA[N2 + N * b + i];
-          su = fma(me[i], xu, su); sc = fma(md[i], xu, sc); sd = fma(me[i], xn, sd);
-        }
-        double *o = RB + qrow + Nm * b;
-        o[0] = su; o[pl] = sc; o[2 * pl] = sd;
-      }
-    }
-    __syncwarp();
-    if (qsub < SQ) {
-      double me[N], md[N];
-#pragma unroll
-      for (int i = 0; i < N; i++) { me[i] = __ldg(Eb + qrow * N + i); md[i] = __ldg(EbD + qrow * N + i); }
-      double *Wr = A.W + R.w_own;
-      for (int qa = qsub; qa < Nm; qa += SQ) {
-        double su = 0., sa = 0., sb = 0., sn = 0.;
-#pragma unroll
-        for (int i = 0; i < N; i++) {
-          const double x1 = RB[qa + Nm * i], x2 = RB[pl + qa + Nm * i], x3 = RB[2 * pl + qa + Nm * i];
-          su = fma(me[i], x1, su); sa = fma(me[i], x2, sa); sb = fma(md[i], x1, sb); sn = fma(me[i], x3, sn);
-        }
-        const int q = qa + Nm * qrow;
-        Wr[q] = su;
-        Wr[Nm2 + q] = __ldg(F + ia * Nm2 + q) * sa + __ldg(F + ib * Nm2 + q) * sb + __ldg(F + d * Nm2 + q) * sn;
-      }
-    }
-    __syncwarp();
   }
+}
+
+/* flux, Galerkin integral and back-projection of one record into the per-face accumulators Y, Z */
+template <int N, int Nq, int NMT>
+__device__ __forceinline__ void tp_flux_record(const tp_args &A, const tp_rec &R, double *YZ, double *RA, double *RB, int lane)
+{
+  using L = HL<N, Nq>;
+  constexpr int N2 = L::N2;
+  const d4b_ops_dev &ops = c_hp_ops[A.qt];
+  const double *pool = ops.pool;
+  const int fm = R.code & 7, tc = (R.code >> 6) & 7, cm = ((R.code >> 9) & 7) - 1;
+  const bool bnd = (R.code >> 15) & 1;
+  const int Nm = NMT ? NMT : R.dims, Nm2 = Nm * Nm, mdq = Nm - 1;
+  const int d = fm >> 1;
+  const int ca = cm < 0 ? 0 : 1 + (cm & 1), cb = cm < 0 ? 0 : 1 + ((cm >> 1) & 1);
+  const double *Ea = pool + ops.idx.I[N - 1][mdq][ca], *EaD = pool + ops.idx.ID[N - 1][mdq][ca];
+  const double *Eb = pool + ops.idx.I[N - 1][mdq][cb], *EbD = pool + ops.idx.ID[N - 1][mdq][cb];
+  const double *F = A.fac + R.fac_off;
+  const double *Wo = A.W + R.w_own, *Wt = A.W + (bnd ? R.w_own : R.w_twin);
+  /* FLUX at the mortar quadrature points (..._flux_sipg.c:645-677 interior, :139-191 Dirichlet, :377-476 Robin) */
+  {
+    const double *wq = pool + ops.idx.w[mdq];
+    for (int q = lane; q < Nm2; q += 32) {
+      const int b = q / Nm, a = q - b * Nm;
+      const double w = __ldg(wq + a) * __ldg(wq + b);
+      const double am0 = __ldg(F + q), am1 = __ldg(F + Nm2 + q), am2 = __ldg(F + 2 * Nm2 + q);
+      const double um = __ldg(Wo + q), qm = __ldg(Wo + Nm2 + q);
+      double jump, t1, sjs, hs;
+      if (!bnd) {
+        const int qp = hp_tcode_src(tc, Nm, a, b);   /* my point in the twin's point order */
+        jump = um - __ldg(Wt + qp); t1 = -0.5 * (qm - __ldg(Wt + Nm2 + qp)); sjs = __ldg(F + 6 * Nm2 + q); hs = -0.5;
+      } else {
+        const double gv = R.g_off >= 0 ? __ldg(A.bc_g + R.g_off + q) : 0.;
+        jump = um - gv; t1 = -qm; sjs = __ldg(F + 3 * Nm2 + q); hs = -1.0;
+        if ((R.code >> 16) & 1) {
+          RB[q] = w * (sjs * um - gv); RB[Nm2 + q] = 0.; RB[2 * Nm2 + q] = 0.; RB[3 * Nm2 + q] = 0.;
+          continue;
+        }
+      }
+      const double wj = w * hs * jump;
+      RB[q] = w * (t1 + sjs * jump);
+      RB[Nm2 + q] = wj * (d == 0 ? am1 : am0);
+      RB[2 * Nm2 + q] = wj * (d == 2 ? am1 : am2);
+      RB[3 * Nm2 + q] = wj * (d == 0 ? am0 : (d == 1 ? am1 : am2));
+    }
+  }
+  __syncwarp();
+  const int NmN = Nm * N;
+  constexpr int SN = 32 / N;
+  const int jrow = lane % N, jsub = lane / N;
+  if (jsub < SN) {
+    for (int qa = jsub; qa < Nm; qa += SN) {
+      double x1 = 0., ha = 0., hn = 0.;
+      const double *f0 = RB + qa;
+#pragma unroll (NMT ? NMT : 4)
+      for (int qb = 0; qb < Nm; qb++) {
+        const double e = __ldg(Eb + qb * N + jrow), ed = __ldg(EbD + qb * N + jrow);
+        const double v0 = f0[Nm * qb], v1 = f0[Nm2 + Nm * qb], v2 = f0[2 * Nm2 + Nm * qb], v3 = f0[3 * Nm2 + Nm * qb];
+        x1 = fma(e, v0, x1); x1 = fma(ed, v2, x1); ha = fma(e, v1, ha); hn = fma(e, v3, hn);
+      }
+      double *o = RA + qa + Nm * jrow;
+      o[0] = x1; o[NmN] = ha; o[2 * NmN] = hn;
+    }
+  }
+  __syncwarp();
+  if (jsub < SN) {
+    double *yz = YZ + fm * 2 * N2;
+    for (int bp = jsub; bp < N; bp += SN) {
+      double y = 0., z = 0.;
+      const double *x1 = RA + Nm * bp;
+#pragma unroll (NMT ? NMT : 4)
+      for (int qa = 0; qa < Nm; qa++) {
+        const double e = __ldg(Ea + qa * N + jrow), ed = __ldg(EaD + qa * N + jrow);
+        y = fma(e, x1[qa], y); y = fma(ed, x1[NmN + qa], y); z = fma(e, x1[2 * NmN + qa], z);
+      }
+      yz[jrow + N * bp] += y; yz[N2 + jrow + N * bp] += z;
+    }
+  }
+  __syncwarp();
 }
 
 template <int N, int Nq>
@@ -648,85 +742,20 @@ __global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_tp_flux_kernel(cons
   double *ACC = sm + (size_t)warp * A.per_warp, *YZ = ACC + L::UA, *RA = YZ + 12 * N2, *RB = RA + 3 * A.NMX * N;
   const tp_slot sl = A.slots[slot];
   for (int i = lane; i < 12 * N2; i += 32) YZ[i] = 0.;
-  const d4b_ops_dev &ops = c_hp_ops[A.qt];
-  const double *pool = ops.pool;
+  /* the volume result that pass 1 left in Au, requested now, needed at the LIFT */
+  double *Aue = A.Au + sl.node_off;
+  for (int i = lane; i < N3; i += 32) ACC[(i % N) + SJ * ((i / N) % N) + SK * (i / N2)] = Aue[i];
 #pragma unroll 1
   for (int r = 0; r < sl.nrec; r++) {
     const tp_rec R = A.recs[sl.rec_begin + r];
-    const int fm = R.code & 7, tc = (R.code >> 6) & 7, cm = ((R.code >> 9) & 7) - 1;
-    const bool bnd = (R.code >> 15) & 1;
-    const int Nm = R.dims, Nm2 = Nm * Nm, mdq = Nm - 1;
-    const int d = fm >> 1;
-    const int ca = cm < 0 ? 0 : 1 + (cm & 1), cb = cm < 0 ? 0 : 1 + ((cm >> 1) & 1);
-    const double *Ea = pool + ops.idx.I[N - 1][mdq][ca], *EaD = pool + ops.idx.ID[N - 1][mdq][ca];
-    const double *Eb = pool + ops.idx.I[N - 1][mdq][cb], *EbD = pool + ops.idx.ID[N - 1][mdq][cb];
-    const double *F = A.fac + R.fac_off;
-    const double *Wo = A.W + R.w_own, *Wt = A.W + (bnd ? R.w_own : R.w_twin);
-    /* FLUX at the mortar quadrature points (..._flux_sipg.c:645-677 interior, :139-191 Dirichlet, :377-476 Robin) */
-    {
-      const double *wq = pool + ops.idx.w[mdq];
-      for (int q = lane; q < Nm2; q += 32) {
-        const int b = q / Nm, a = q - b * Nm;
-        const double w = __ldg(wq + a) * __ldg(wq + b);
-        const double am0 = __ldg(F + q), am1 = __ldg(F + Nm2 + q), am2 = __ldg(F + 2 * Nm2 + q);
-        const double um = __ldg(Wo + q), qm = __ldg(Wo + Nm2 + q);
-        double jump, t1, sjs, hs;
-        if (!bnd) {
-          const int qp = hp_tcode_src(tc, Nm, a, b);   /* my point in the twin's point order */
-          jump = um - __ldg(Wt + qp); t1 = -0.5 * (qm - __ldg(Wt + Nm2 + qp)); sjs = __ldg(F + 6 * Nm2 + q); hs = -0.5;
-        } else {
-          const double gv = R.g_off >= 0 ? __ldg(A.bc_g + R.g_off + q) : 0.;
-          jump = um - gv; t1 = -qm; sjs = __ldg(F + 3 * Nm2 + q); hs = -1.0;
-          if ((R.code >> 16) & 1) {
-            RB[q] = w * (sjs * um - gv); RB[Nm2 + q] = 0.; RB[2 * Nm2 + q] = 0.; RB[3 * Nm2 + q] = 0.;
-            continue;
-          }
-        }
-        const double wj = w * hs * jump;
-        RB[q] = w * (t1 + sjs * jump);
-        RB[Nm2 + q] = wj * (d == 0 ? am1 : am0);
-        RB[2 * Nm2 + q] = wj * (d == 2 ? am1 : am2);
-        RB[3 * Nm2 + q] = wj * (d == 0 ? am0 : (d == 1 ? am1 : am2));
-      }
+    switch (R.dims - Nq) {
+      case 0: tp_flux_record<N, Nq, Nq>(A, R, YZ, RA, RB, lane); break;
+      case 1: tp_flux_record<N, Nq, Nq + 1>(A, R, YZ, RA, RB, lane); break;
+      case 2: tp_flux_record<N, Nq, Nq + 2>(A, R, YZ, RA, RB, lane); break;
+      default: tp_flux_record<N, Nq, 0>(A, R, YZ, RA, RB, lane); break;
     }
-    __syncwarp();
-    const int NmN = Nm * N;
-    constexpr int SN = 32 / N;
-    const int jrow = lane % N, jsub = lane / N;
-    if (jsub < SN) {
-      for (int qa = jsub; qa < Nm; qa += SN) {
-        double x1 = 0., ha = 0., hn = 0.;
-        const double *f0 = RB + qa;
-#pragma unroll 4
-        for (int qb = 0; qb < Nm; qb++) {
-          const double e = __ldg(Eb + qb * N + jrow), ed = __ldg(EbD + qb * N + jrow);
-          const double v0 = f0[Nm * qb], v1 = f0[Nm2 + Nm * qb], v2 = f0[2 * Nm2 + Nm * qb], v3 = f0[3 * Nm2 + Nm * qb];
-          x1 = fma(e, v0, x1); x1 = fma(ed, v2, x1); ha = fma(e, v1, ha); hn = fma(e, v3, hn);
-        }
-        double *o = RA + qa + Nm * jrow;
-        o[0] = x1; o[NmN] = ha; o[2 * NmN] = hn;
-      }
-    }
-    __syncwarp();
-    if (jsub < SN) {
-      double *yz = YZ + fm * 2 * N2;
-      for (int bp = jsub; bp < N; bp += SN) {
-        double y = 0., z = 0.;
-        const double *x1 = RA + Nm * bp;
-#pragma unroll 4
-        for (int qa = 0; qa < Nm; qa++) {
-          const double e = __ldg(Ea + qa * N + jrow), ed = __ldg(EaD + qa * N + jrow);
-          y = fma(e, x1[qa], y); y = fma(ed, x1[NmN + qa], y); z = fma(e, x1[2 * NmN + qa], z);
-        }
-        yz[jrow + N * bp] += y; yz[N2 + jrow + N * bp] += z;
-      }
-    }
-    __syncwarp();
   }
   /* LIFT onto the volume result that pass 1 left in Au */
-  double *Aue = A.Au + sl.node_off;
-  for (int i = lane; i < N3; i += 32) ACC[(i % N) + SJ * ((i / N) % N) + SK * (i / N2)] = Aue[i];
-  __syncwarp();
 #pragma unroll 1
   for (int d = 0; d < 3; d++) {
     int sa, sb, sn; hp_face_strides(d, SJ, SK, sa, sb, sn);
