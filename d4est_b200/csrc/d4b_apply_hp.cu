@@ -462,6 +462,12 @@ __global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_apply_hp_kernel(con
  * disappear; what is added is 2 Nm^2 doubles written and 4 Nm^2 read per record.  Elements with a ghost neighbour
  * keep the single-pass kernel above (the twin's trace lives on another rank).  Pass 1 also runs, trace only, over
  * the local neighbours of two-pass elements that are handled by other kernels. */
+#ifndef TP_TRACE_MINB
+#define TP_TRACE_MINB(N) ((N) <= 4 ? 8 : ((N) <= 6 ? 5 : 4))
+#endif
+#ifndef TP_FLUX_MINB
+#define TP_FLUX_MINB(N) ((N) <= 4 ? 8 : ((N) <= 6 ? 6 : 4))
+#endif
 struct tp_rec {        /* 48 bytes */
   int64_t fac_off, g_off, w_own, w_twin;   /* w_twin < 0: boundary */
   int32_t code;        /* bits 0-2 f_m, 6-8 tcode, 9-11 child_m+1, 15 boundary, 16 Robin */
@@ -545,7 +551,7 @@ __device__ __forceinline__ void tp_trace_record(const tp_args &A, const tp_rec &
 }
 
 template <int N, int Nq>
-__global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_tp_trace_kernel(const tp_args A)
+__global__ void __launch_bounds__(128, TP_TRACE_MINB(N)) d4b_tp_trace_kernel(const tp_args A)
 {
   using L = HL<N, Nq>;
   constexpr int N2 = L::N2, N3 = L::N3, Q2 = L::Q2, Q3 = L::Q3, NQ = L::NQ;
@@ -729,7 +735,7 @@ __device__ __forceinline__ void tp_flux_record(const tp_args &A, const tp_rec &R
 }
 
 template <int N, int Nq>
-__global__ void __launch_bounds__(128, (N <= 4 ? 5 : 4)) d4b_tp_flux_kernel(const tp_args A)
+__global__ void __launch_bounds__(128, TP_FLUX_MINB(N)) d4b_tp_flux_kernel(const tp_args A)
 {
   using L = HL<N, Nq>;
   constexpr int N2 = L::N2, N3 = L::N3, SJ = L::SJ, SK = L::SK;
