@@ -536,15 +536,16 @@ __device__ __forceinline__ void tp_trace_record(const tp_args &A, const tp_rec &
     for (int i = 0; i < N; i++) { me[i] = __ldg(Eb + qrow * N + i); md[i] = __ldg(EbD + qrow * N + i); }
     double *Wr = A.W + R.w_own;
     for (int qa = qsub; qa < Nm; qa += SQ) {
+      const int q = qa + Nm * qrow;
+      const double fa = __ldg(F + ia * Nm2 + q), fb = __ldg(F + ib * Nm2 + q), fn = __ldg(F + d * Nm2 + q);
       double su = 0., sa = 0., sb = 0., sn = 0.;
 #pragma unroll
       for (int i = 0; i < N; i++) {
         const double x1 = RB[qa + Nm * i], x2 = RB[pl + qa + Nm * i], x3 = RB[2 * pl + qa + Nm * i];
         su = fma(me[i], x1, su); sa = fma(me[i], x2, sa); sb = fma(md[i], x1, sb); sn = fma(me[i], x3, sn);
       }
-      const int q = qa + Nm * qrow;
       Wr[q] = su;
-      Wr[Nm2 + q] = __ldg(F + ia * Nm2 + q) * sa + __ldg(F + ib * Nm2 + q) * sb + __ldg(F + d * Nm2 + q) * sn;
+      Wr[Nm2 + q] = fa * sa + fb * sb + fn * sn;
     }
   }
   __syncwarp();
@@ -643,15 +644,18 @@ __global__ void __launch_bounds__(128, TP_TRACE_MINB(N)) d4b_tp_trace_kernel(con
 
   /* ---------------- own-side traces of the records: T -> S1 -> QV -> W */
   double *RA = S, *RB = S + 2 * N2;
+  tp_rec R = A.recs[sl.rec_begin];
 #pragma unroll 1
   for (int r = 0; r < sl.nrec; r++) {
-    const tp_rec R = A.recs[sl.rec_begin + r];
+    tp_rec Rn = R;   /* the next record is requested now and used in the next iteration */
+    if (r + 1 < sl.nrec) Rn = A.recs[sl.rec_begin + r + 1];
     switch (R.dims - Nq) {
       case 0: tp_trace_record<N, Nq, Nq>(A, R, U, RA, RB, D, lane); break;
       case 1: tp_trace_record<N, Nq, Nq + 1>(A, R, U, RA, RB, D, lane); break;
       case 2: tp_trace_record<N, Nq, Nq + 2>(A, R, U, RA, RB, D, lane); break;
       default: tp_trace_record<N, Nq, 0>(A, R, U, RA, RB, D, lane); break;
     }
+    R = Rn;
   }
 }
 
@@ -750,17 +754,26 @@ __global__ void __launch_bounds__(128, TP_FLUX_MINB(N)) d4b_tp_flux_kernel(const
   for (int i = lane; i < 12 * N2; i += 32) YZ[i] = 0.;
   /* the volume result that pass 1 left in Au, requested now, needed at the LIFT */
   double *Aue = A.Au + sl.node_off;
-  for (int i = lane; i < N3; i += 32) ACC[(i % N) + SJ * ((i / N) % N) + SK * (i / N2)] = Aue[i];
+  for (int i = lane; i < N3; i += 32) {   /* asynchronous: nothing waits for it before the LIFT */
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(ACC + (i % N) + SJ * ((i / N) % N) + SK * (i / N2));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(Aue + i) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  tp_rec R = A.recs[sl.rec_begin];
 #pragma unroll 1
   for (int r = 0; r < sl.nrec; r++) {
-    const tp_rec R = A.recs[sl.rec_begin + r];
+    tp_rec Rn = R;   /* the next record is requested now and used in the next iteration */
+    if (r + 1 < sl.nrec) Rn = A.recs[sl.rec_begin + r + 1];
     switch (R.dims - Nq) {
       case 0: tp_flux_record<N, Nq, Nq>(A, R, YZ, RA, RB, lane); break;
       case 1: tp_flux_record<N, Nq, Nq + 1>(A, R, YZ, RA, RB, lane); break;
       case 2: tp_flux_record<N, Nq, Nq + 2>(A, R, YZ, RA, RB, lane); break;
       default: tp_flux_record<N, Nq, 0>(A, R, YZ, RA, RB, lane); break;
     }
+    R = Rn;
   }
+  asm volatile("cp.async.wait_all;" ::: "memory");
+  __syncwarp();
   /* LIFT onto the volume result that pass 1 left in Au */
 #pragma unroll 1
   for (int d = 0; d < 3; d++) {
