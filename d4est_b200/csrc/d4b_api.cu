@@ -37,6 +37,7 @@ static void opts_init()
   g_opt.init = true;
 }
 extern int g_fcg_textbook;   /* d4b_solver.cu */
+extern int g_mg_graph;       /* d4b_mg.cu */
 int d4b_opt_tp_min() { opts_init(); return g_opt.tp_min; }   /* d4b_apply_hp.cu */
 
 extern "C" {
@@ -51,6 +52,7 @@ int d4b_set_option(const char *name, int value)
   else if (!strcmp(name, "pipe_trace")) g_opt.pipe_trace = value;
   else if (!strcmp(name, "pipe_chunks")) g_opt.pipe_chunks = value;
   else if (!strcmp(name, "no_overlap")) g_opt.no_overlap = value;
+  else if (!strcmp(name, "mg_graph")) g_mg_graph = value;
   else if (!strcmp(name, "two_pass_min_elements")) g_opt.tp_min = value;         /* read when a level is created */
   else if (!strcmp(name, "overlap_min_elements")) g_opt.overlap_min = value;   /* read when a level first exchanges */
   else { d4b_set_error("unknown option %s", name); return D4B_EINVAL; }

@@ -100,6 +100,29 @@ def test_mg_fcg_solve_matches_reference_iteration_count(mgfx):
     assert rel(u, fx["mg_u_ref"]) < 1e-6
 
 
+def test_cuda_graph_replay_of_the_preconditioner_is_bitwise_the_plain_path(mgfx):
+    """option "mg_graph": the single-V-cycle preconditioner application captured into a CUDA graph (second call on)
+    replays the same kernels in the same order: same iterates, bit for bit, and far fewer host launches."""
+    fx, levels, tabs, trs, mg, par = mgfx
+    n = levels[-1].local_nodes
+    rhs = np.ascontiguousarray(fx["mg_rhs"])
+    L = lib()
+    out = {}
+    for key, on in (("plain", 0), ("graph", 1)):
+        check(L.d4b_set_option(b"mg_graph", on))
+        try:
+            u = np.zeros(n); it, res = C.c_int(), C.c_double()
+            n0 = L.d4b_kernel_launches()
+            check(L.d4b_mg_fcg_solve_host(mg.handle, u.ctypes.data_as(C.c_void_p), rhs.ctypes.data_as(C.c_void_p), 12,
+                                          0., 1e-300, C.byref(it), C.byref(res)))
+            out[key] = (u, it.value, L.d4b_kernel_launches() - n0)
+        finally:
+            check(L.d4b_set_option(b"mg_graph", 0))
+    assert out["plain"][1] == out["graph"][1] == 12
+    assert np.array_equal(out["plain"][0], out["graph"][0])
+    assert out["graph"][2] < out["plain"][2] // 4, (out["graph"][2], out["plain"][2])
+
+
 def test_d4est_facing_entry_points_in_one_process_with_the_reference():
     """oracle/_ref/d4b_mg_harness --gpu-check: ONE process that holds the unmodified reference and calls, next to
     it, the d4est-facing entry points of the product glue on the GPU: d4est_b200_apply_lhs (d4est_apply_operator_fcn_t),
