@@ -858,8 +858,8 @@ static int tp_find_twin(const d4b_mesh_desc_t *D, int e, int r)
 /* Take the elements of `cand` the templated hp kernels can run (instance exists, neighbour N <= HP_MAXNP,
  * mortar points <= HP_MAXNM, one warp's scratch fits) into (N, Nq) buckets with resolved per-record
  * metadata; the others are appended to `rest` (completeness kernel).  Elements whose neighbours are all local
- * (and have a trace instance) take the two-pass path when the level has enough of them to pay for the second
- * round of launches; the rest (ghost neighbours, small levels) the single-pass kernel. */
+ * (and have a trace instance) take the two-pass path (measured faster down to 300-element levels; the option
+ * two_pass_min_elements can demand a minimum count); the rest (ghost neighbours) the single-pass kernel. */
 int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_t> &cand, std::vector<int32_t> &rest)
 {
   m->n_hp = 0; m->n_tp1 = m->n_tp2 = 0; m->tpW = nullptr; m->tpW_doubles = 0;

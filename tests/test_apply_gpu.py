@@ -47,7 +47,7 @@ def test_hp_kernel_matches_reference_on_every_element_class(path):
     for key, env in (("default", {}), ("all_hp", {"D4B_ALL_HP": "1"}), ("no_hp", {"D4B_NO_HP": "1"}),
                      ("two_pass", {}), ("all_hp_two_pass", {"D4B_ALL_HP": "1"})):
         os.environ.update(env)
-        # the two-pass (twin-trace) hp kernels are chosen for levels with >= 4096 such elements: force them here
+        # two-pass (twin-trace) hp kernels on (the default) or off (single-pass kernel for every hp element)
         d4est_b200.capi.check(L.d4b_set_option(b"two_pass_min_elements", 0 if "two_pass" in key else 1 << 30))
         try:
             lvl = d4est_b200.MeshLevel(fx)
@@ -57,7 +57,7 @@ def test_hp_kernel_matches_reference_on_every_element_class(path):
                 assert np.array_equal(out[key], lvl.apply_host(fx["u"]))   # fixed accumulation order
             lvl.close()
         finally:
-            d4est_b200.capi.check(L.d4b_set_option(b"two_pass_min_elements", 4096))
+            d4est_b200.capi.check(L.d4b_set_option(b"two_pass_min_elements", 0))
             for k in env:
                 del os.environ[k]
     nl = int(fx["hdr"][0])
