@@ -9,7 +9,7 @@
  *      flat tables + u + reference Au to a fixture file (format: oracle/fixture.py),
  *   4. optionally times the reference apply (bench.py cpu_baseline kind "reference").
  *
- * usage: d4b_harness <input> <amr: none|random_hp|uniform_h> <steps> <bc: zero|poly|robin>
+ * usage: d4b_harness <input> <amr: none|random_hp|uniform_h> <steps> <bc: zero|poly|polyquad|robin>
  *                    <u: polyrand|sinrand|poly> <out.fix|-> [timing_reps]
  */
 #include <pXest.h>
@@ -114,7 +114,8 @@ int main(int argc, char **argv)
 
   d4est_laplacian_dirichlet_bc_t bcd;
   bcd.dirichlet_fcn = !strcmp(bc, "zero") ? zero_fcn : poly_fcn;
-  bcd.eval_method = EVAL_BNDRY_FCN_ON_LOBATTO;
+  /* "polyquad": the same polynomial data evaluated directly at the mortar quadrature points (..._flux_sipg.c:125-138) */
+  bcd.eval_method = !strcmp(bc, "polyquad") ? EVAL_BNDRY_FCN_ON_QUAD : EVAL_BNDRY_FCN_ON_LOBATTO;
   bcd.user = NULL;
   d4est_laplacian_robin_bc_t rb0; rb0.robin_coeff = robin_coeff_base; rb0.robin_rhs = robin_rhs_base; rb0.user = NULL;
   d4est_laplacian_with_opt_robin_bc_t rb1; rb1.robin_coeff = robin_coeff_opt; rb1.robin_rhs = robin_rhs_opt; rb1.user = NULL;
