@@ -33,7 +33,7 @@ static void opts_init()
   g_opt.pipe_chunks = getenv("D4B_PIPE_CHUNKS") ? atoi(getenv("D4B_PIPE_CHUNKS")) : 0;
   g_opt.no_overlap = getenv("D4B_NO_OVERLAP") != nullptr;
   g_opt.overlap_min = getenv("D4B_OVERLAP_MIN") ? atoi(getenv("D4B_OVERLAP_MIN")) : 16384;
-  g_opt.tp_min = getenv("D4B_NO_TP") ? 0x7fffffff : (getenv("D4B_TP_MIN") ? atoi(getenv("D4B_TP_MIN")) : 0);
+  g_opt.tp_min = getenv("D4B_NO_TP") ? 0x7fffffff : (getenv("D4B_TP_MIN") ? atoi(getenv("D4B_TP_MIN")) : -1);
   g_opt.init = true;
 }
 extern int g_fcg_textbook;   /* d4b_solver.cu */

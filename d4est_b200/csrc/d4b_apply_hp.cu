@@ -884,7 +884,12 @@ int d4b_hp_build(d4b_mesh *m, const d4b_mesh_desc_t *D, const std::vector<int32_
     el.push_back({e, nmx, mx});
   }
   /* ---- which of them take the two-pass path */
-  const int tp_min = d4b_opt_tp_min();   /* option two_pass_min_elements (D4B_TP_MIN; D4B_NO_TP = never) */
+  /* option two_pass_min_elements (D4B_TP_MIN; D4B_NO_TP = never).  Default (-1): always on a level without neighbour
+   * ranks (measured faster down to 300 elements: 61 against 79 us per apply); with neighbour ranks only from 4 096
+   * two-pass elements up -- there the elements along the rank boundary stay single-pass and small levels pay for
+   * the extra launches (MG-FCG on the 50 k-element hp mesh: 6.15 / 5.01 s at 2 / 4 GPUs, 6.48 / 5.36 s with 0) */
+  int tp_min = d4b_opt_tp_min();
+  if (tp_min < 0) tp_min = D->n_peers > 0 ? 4096 : 0;
   const bool no_tp = tp_min == 0x7fffffff;
   std::vector<char> is_tp(nl, 0);
   std::vector<int32_t> twin(D->hm_begin[nl], -1);

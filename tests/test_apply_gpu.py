@@ -57,7 +57,7 @@ def test_hp_kernel_matches_reference_on_every_element_class(path):
                 assert np.array_equal(out[key], lvl.apply_host(fx["u"]))   # fixed accumulation order
             lvl.close()
         finally:
-            d4est_b200.capi.check(L.d4b_set_option(b"two_pass_min_elements", 0))
+            d4est_b200.capi.check(L.d4b_set_option(b"two_pass_min_elements", -1))   # back to the default rule
             for k in env:
                 del os.environ[k]
     nl = int(fx["hdr"][0])

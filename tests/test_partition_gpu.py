@@ -14,6 +14,19 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["two_pass", "single_pass"])
+def hp_mode(request):
+    """Levels with neighbour ranks take the two-pass hp kernels only from 4 096 elements up by default; these small
+    rank-local levels are run both ways: two-pass for every element whose neighbours are local (the elements along
+    the rank boundary stay single-pass and feed traces to their two-pass neighbours), and single-pass throughout."""
+    L = d4est_b200.lib()
+    d4est_b200.capi.check(L.d4b_set_option(b"two_pass_min_elements", 0 if request.param == "two_pass" else 1 << 30))
+    os.environ["D4B_TP_MIN"] = "0" if request.param == "two_pass" else str(1 << 30)   # for the NCCL worker processes
+    yield request.param
+    d4est_b200.capi.check(L.d4b_set_option(b"two_pass_min_elements", -1))
+    del os.environ["D4B_TP_MIN"]
+
+
 def _fix(name, golden_dir, ref_fixture_dir):
     for d in (golden_dir, ref_fixture_dir):
         p = os.path.join(d, name + ".fix")
