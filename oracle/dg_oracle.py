@@ -128,12 +128,54 @@ def _E(deg, degq, qt, child):
 
 
 # ---------------------------------------------------------------- the apply
-def apply(fx, u, u_ghost=None):
+def twin_records(fx):
+    """twin[r] = the record of the neighbour that shares the mortar of record r with the roles swapped (same faces,
+    child indices exchanged, same mortar degree), or -1 (boundary, ghost neighbour)."""
+    nl = int(fx["hdr"][0]); hm, hb = fx["hm"], fx["hm_begin"]
+    key = {}
+    for e in range(nl):
+        for r in range(hb[e], hb[e + 1]):
+            h = hm[r]
+            key[(e, int(h["nbr"]), int(h["f_m"]), int(h["f_p"]), int(h["child_m"]), int(h["child_p"]), int(h["degq"]))] = r
+    twin = np.full(int(hb[nl]), -1, np.int64)
+    for e in range(nl):
+        for r in range(hb[e], hb[e + 1]):
+            h = hm[r]; p = int(h["nbr"])
+            if 0 <= p < nl:
+                twin[r] = key.get((p, e, int(h["f_p"]), int(h["f_m"]), int(h["child_p"]), int(h["child_m"]), int(h["degq"])), -1)
+    return twin
+
+
+def own_traces(fx, u):
+    """Pass 1 of the two-pass form (d4b_tp_trace_kernel): per record the own-side trace at the mortar points,
+    (u-, sum_l a-_l du-/dr_l), in the element's own point order."""
+    nl, _, qt, _ = [int(v) for v in fx["hdr"]]
+    deg, node_off, hm, hb, fac = fx["deg"], fx["node_off"], fx["hm"], fx["hm_begin"], fx["fac"]
+    W = [None] * int(hb[nl])
+    for e in range(nl):
+        dg = int(deg[e]); N = dg + 1; D = diff_matrix(dg)
+        ue = u[node_off[e]:node_off[e + 1]]
+        for r in range(hb[e], hb[e + 1]):
+            h = hm[r]; mdq = int(h["degq"]); Nm = mdq + 1; n2 = Nm * Nm
+            Ea, Eb = _E(dg, mdq, qt, int(h["child_m"]))
+            fm = _face_fields(ue, N, int(h["f_m"]), D)
+            mq = np.einsum("qa,pb,cba->cpq", Ea, Eb, fm.reshape(4, N, N)).reshape(4, n2)
+            am = fac[h["fac_off"]:][:3 * n2].reshape(3, n2)
+            W[r] = (mq[0], (am * mq[1:]).sum(0))
+    return W
+
+
+def apply(fx, u, u_ghost=None, twin_traces=False):
     """Au = A u.  Restates d4est_laplacian_with_opt_apply_aij
     (dGMath/d4est_laplacian_with_opt.c:289-368) in the one-side-at-a-time form of its twin
     d4est_laplacian_apply_aij (dGMath/d4est_laplacian.c:317; the two agree to 1e-13,
-    Tests/Unit/d4est_test_laplacian_speedup.c:485)."""
+    Tests/Unit/d4est_test_laplacian_speedup.c:485).
+    twin_traces=True: the neighbour side of an interior record with a local neighbour is taken from the own-side
+    trace of the neighbour's twin record, u+ = W[twin].u, sum a+ du+ = -W[twin].q (reordered by the orientation
+    code) -- the formulation of the two-pass device kernels; a+ = -a-(twin) holds at the same physical points."""
     nl, ng, qt, _ = [int(v) for v in fx["hdr"]]
+    twin = twin_records(fx) if twin_traces else None
+    Wtr = own_traces(fx, u) if twin_traces else None
     deg, degq, node_off, quad_off = fx["deg"], fx["degq"], fx["node_off"], fx["quad_off"]
     hm, hb, fac, bcg, G = fx["hm"], fx["hm_begin"], fx["fac"], fx["bc_g"], fx["G"]
     local_nodes = int(node_off[nl])
@@ -166,7 +208,12 @@ def apply(fx, u, u_ghost=None):
             F = fac[h["fac_off"]:]
             am = F[:3 * n2].reshape(3, n2)
             qm = (am * mq[1:]).sum(0)
-            if h["nbr"] >= 0:
+            if h["nbr"] >= 0 and twin_traces and twin[r] >= 0:
+                perm = tcode_perm(int(h["tcode"]), Nm)
+                sjs = F[6 * n2:7 * n2]
+                jump = mq[0] - Wtr[twin[r]][0][perm]
+                t1 = -0.5 * (qm - Wtr[twin[r]][1][perm]); hs = -0.5
+            elif h["nbr"] >= 0:
                 nb = int(h["nbr"]); dp = int(deg[nb]); Np = dp + 1
                 un = uext[node_off[nb]:node_off[nb + 1]]
                 Pa, Pb = _E(dp, mdq, qt, int(h["child_p"]))

@@ -203,3 +203,20 @@ def test_amr_field_transfer_oracle_matches_reference(golden_dir):
         if k + 1 < steps:   # the reference chains the steps: its output is the next step's input, bit for bit
             assert np.array_equal(ref, fx[f"S{k + 1}.field_pre"])
     assert {"h", "p", "balance_h"} <= kinds   # the fixture exercises h-, p-refinement and the 2:1 balance sweep
+
+
+@pytest.mark.parametrize("name", ["cubed_sphere_hp1", "brick_p3_l2"])
+def test_twin_trace_formulation_equals_the_reference(golden_dir, name):
+    """The identity the two-pass device kernels rest on, on the CPU: taking the neighbour side of every interior
+    half-mortar from the own-side trace of the neighbour's twin record (u+ = W[twin].u, sum a+ du+ = -W[twin].q)
+    reproduces the reference's Au; every interior record of a one-rank mesh has a twin, hanging and mixed-p included."""
+    fx = fixture.load(os.path.join(golden_dir, name + ".fix"))
+    nl = int(fx["hdr"][0])
+    twin = dg_oracle.twin_records(fx)
+    interior = np.array([0 <= int(h["nbr"]) < nl for h in fx["hm"][:int(fx["hm_begin"][nl])]])
+    assert (twin[interior] >= 0).all() and (twin[~interior] < 0).all()
+    assert (twin[twin[interior]] == np.nonzero(interior)[0]).all()      # an involution
+    Au = dg_oracle.apply(fx, fx["u"], twin_traces=True)
+    ref = fx["Au_ref_with_opt"]
+    assert np.linalg.norm(Au - ref) / np.linalg.norm(ref) < 1e-12
+    assert np.linalg.norm(Au - dg_oracle.apply(fx, fx["u"])) / np.linalg.norm(ref) < 1e-13
