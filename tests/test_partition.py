@@ -32,6 +32,25 @@ def test_rank_local_apply_equals_serial(brick, nranks):
     assert seen == fx["u"].size
 
 
+def test_rank_local_twin_trace_apply_equals_reference(golden_dir):
+    """The two-pass formulation on rank-local tables of the curved hp mesh (3 ranks): records whose neighbour is a
+    ghost have no local twin and take the neighbour side directly from the halo (on the device: the single-pass
+    kernel), every other interior record takes it from the twin's trace; the result is the reference's Au."""
+    fx = fixture.load(os.path.join(golden_dir, "cubed_sphere_hp1.fix"))
+    ref = fx["Au_ref_with_opt"]
+    n_twin = n_ghost_side = 0
+    for me in P.partition(fx, 3):
+        a, b = me["node_range"]
+        nl = int(me["hdr"][0])
+        tw = dg_oracle.twin_records(me)
+        nbr = me["hm"]["nbr"][:int(me["hm_begin"][nl])]
+        assert ((tw >= 0) == ((nbr >= 0) & (nbr < nl))).all()
+        n_twin += int((tw >= 0).sum()); n_ghost_side += int((nbr >= nl).sum())
+        Au = dg_oracle.apply(me, P.local_vector(fx, me, fx["u"]), P.ghost_vector(fx, me, fx["u"]), twin_traces=True)
+        assert np.linalg.norm(Au - ref[a:b]) <= 1e-12 * np.linalg.norm(ref[a:b])
+    assert n_twin > 0 and n_ghost_side > 0
+
+
 def test_halo_lists_are_consistent(golden_dir):
     """What rank r sends to p is exactly, and in order, what p holds as ghosts owned by r (curved hp mesh)."""
     fx = fixture.load(os.path.join(golden_dir, "cubed_sphere_hp1.fix"))
